@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""bench.py -- decode throughput of the B200 GGUF engine on BASELINE.json's headline config.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one decode step (one new token for one sequence: every weight matrix streamed
+once, attention over the cached context).  Workload at N=1 = BASELINE.json configs[1]:
+llama2-7B Q4_0 (synthetic random-init GGUF, Q6_K head as in the shipped files), batch 1,
+decode after a 512-token prefill.  With N>1 every rank is an independent replica on its own
+B200 (the reference's only parallelism: `spec.replicas`, pkg/model/model.go:72) -- weak
+scaling, no data-path collective; `value` is the sum over replicas.
+
+  value   device-resident greedy loop (b2_decode_greedy): tokens, positions and KV stay in HBM
+  e2e     the same steps through b2_decode with HOST token buffers (H2D + D2H every step)
+  roofline dominant kernel = the fused W4A8 GEMV; achieved = weight bytes of the largest
+          per-layer matrix (gate|up, 22016x4096 Q4_0) / its mean launch time, timed alone
+          with CUDA events on its stream, against the measured burst HBM peak; `step` adds
+          the whole-step figure against the same peak
+  cpu_baseline  the CPU oracle (oracle/ggml_ref.c, a port of the llama.cpp CPU path) timed on
+          the host cores for a bounded sample of the same workload; also used to check the
+          GPU logits/tokens at full model size
+
+`--impl reference` times that CPU path alone with all host threads (the reference's own
+container cannot run here: no Go/docker/ollama).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "decode_tokens_per_s"
+UNIT = "tok/s"
+
+
+def pkg():
+    return importlib.import_module("ollama-operator_b200")
+
+
+def oracle_mod():
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle
+    oracle.lib()
+    return oracle
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def model_path(args):
+    p = pkg()
+    t0 = time.time()
+    path = p.synth.cached_model(args.model, source="blocks")
+    return path, time.time() - t0
+
+
+def run_reference(args):
+    """CPU arm: the oracle port of the llama.cpp CPU path, all host threads, same config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    p, o = pkg(), oracle_mod()
+    path, _ = model_path(args)
+    cfg = p.synth.PRESETS[args.model]
+    om = o.OracleModel(path, faithful=True, n_ctx=args.ctx + args.steps + args.warmup + 8)
+    kvd = cfg.n_head_kv * cfg.head_dim
+    rng = np.random.default_rng(99)
+    # A 512-token CPU prefill would take minutes; decode speed does not depend on the cached
+    # values, so the context is a synthetic f16 prefix.
+    for il in range(cfg.n_layer):
+        kv = (rng.standard_normal((2, args.ctx, kvd)) * 0.5).astype(np.float16)
+        om.set_kv(il, kv[0], kv[1])
+    tok, pos = 1, args.ctx
+    for _ in range(args.warmup):
+        tok = int(np.argmax(om.eval(tok, pos))); pos += 1
+    steps, t0 = 0, time.perf_counter()
+    budget_s = float(os.environ.get("B2_REF_BUDGET_S", "150"))
+    while steps < args.steps:
+        tok = int(np.argmax(om.eval(tok, pos))); pos += 1; steps += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    v = steps / dt
+    cores = o.lib().ref_num_threads()
+    sample = f"{steps} decode steps at ctx {args.ctx} (synthetic f16 KV prefix), {args.warmup} warm-up"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8xint4->f32",
+        "data": "synthetic", "config": workload_config(args, cfg),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(args, cfg):
+    return {"workload": f"{args.model} {cfg.ftype.upper()} (Q6_K head) batch-1 decode after a {args.ctx}-token prefill",
+            "batch": 1, "context": args.ctx, "parallelism": f"replicas x{args.gpus} (one engine per GPU, no collective)",
+            "l2": "inputs larger than L2: 3.8 GB of weights streamed per step vs 126 MB L2"}
+
+
+def run_gpu(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    p = pkg()
+    cfg = p.synth.PRESETS[args.model]
+    if rank == 0 or world == 1:
+        path, gen_s = model_path(args)
+    if dist:
+        dist.barrier()
+        path, gen_s = model_path(args)      # cached by rank 0
+    E = p.engine
+    eng = E.Engine(local)
+    t0 = time.time()
+    m = eng.load(path, max_batch=1, max_ctx=args.ctx + 2 * (args.steps + args.warmup) + 64)
+    load_s = time.time() - t0
+    info = m.info
+    prompt = p.synth.prompt_tokens(args.ctx, info.n_vocab)
+    seq = m.seq_new()
+    logits0 = m.prefill(seq, prompt)
+    prefill_ms = m.stats().gpu_ms
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident loop: `value` ------------------------------------------------------------
+    m.decode_greedy(seq, args.warmup)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    toks = m.decode_greedy(seq, args.steps)
+    st = m.stats()
+    barrier()
+    gpu_ms, launches = st.gpu_ms, int(st.last_launches)
+    clocks = sampler.stop()
+    ctx_mid = args.ctx + args.warmup + args.steps // 2
+    # ---- end to end through b2_decode with host buffers: `e2e` ---------------------------------------
+    last = int(toks[-1])
+    for _ in range(3):
+        last = int(m.decode([seq], [last])[0])
+    barrier()
+    t0 = time.perf_counter()
+    e2e_gpu_ms = 0.0
+    for _ in range(args.steps):
+        last = int(m.decode([seq], [last])[0])
+        e2e_gpu_ms += m.stats().gpu_ms
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    tmax = torch.tensor([gpu_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
+    if dist:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    gpu_ms_max, e2e_ms_max = float(tmax[0]), float(tmax[1])
+    if rank != 0:
+        m.close(); eng.close()
+        if dist:
+            dist.destroy_process_group()
+        return
+
+    value = world * args.steps / (gpu_ms_max / 1e3)
+    e2e = world * args.steps / (e2e_ms_max / 1e3)
+    peak, peak_src = peaks()
+    # ---- dominant kernel, timed alone (CUDA events on its stream, L2-cold operands) -------------------
+    rows_up = 2 * cfg.n_ff if cfg.arch == "llama" else cfg.n_ff
+    body_type = {"q4_0": E.TYPE_Q4_0, "q8_0": E.TYPE_Q8_0, "q4_k_m": E.TYPE_Q4_K}[cfg.ftype]
+    bpw = {E.TYPE_Q4_0: 18 / 32, E.TYPE_Q8_0: 34 / 32, E.TYPE_Q4_K: 144 / 256}[body_type]
+    k_ms = E.gemv_bench(body_type, rows_up, cfg.n_embd, iters=200)
+    k_bytes = rows_up * cfg.n_embd * bpw
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    step_bytes = info.step_weight_bytes + ctx_mid * info.kv_bytes_per_token
+    step_gbs = step_bytes / (gpu_ms / args.steps * 1e-3) / 1e9
+    prof = m.profile_step(seq, last)
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": gpu_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int8xint4->f32", "data": "synthetic", "config": workload_config(args, cfg),
+        "clocks": clocks, "gpu_launches": launches,
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4,
+                "gpu_ms_per_step": e2e_gpu_ms / args.steps},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": f"gemv_kernel<Q4_0> gate|up {rows_up}x{cfg.n_embd}", "bytes_per_launch": k_bytes, "ms_per_launch": k_ms,
+                     "peak_source": peak_src,
+                     "step": {"bytes": step_bytes, "achieved": step_gbs, "frac": step_gbs / peak}},
+        "profile_step_ms": {k: round(v[0], 4) for k, v in prof.items()},
+        "prefill": {"tokens": args.ctx, "ms": prefill_ms, "note": "token-by-token through the decode kernels"},
+        "setup_s": {"write_gguf": round(gen_s, 1), "load": round(load_s, 1)},
+    }
+    if world == 1 and not args.no_cpu:
+        out["cpu_baseline"], out["parity"] = cpu_baseline(args, p, m, seq, path, cfg)
+    m.close(); eng.close()
+    if dist:
+        dist.destroy_process_group()
+    print(json.dumps(out))
+
+
+def cpu_baseline(args, p, m, seq, path, cfg):
+    """Bounded CPU sample: continue the SAME sequence on the host from the GPU's KV cache, time it,
+    and use it to check the GPU's logits and greedy tokens at full model size."""
+    o = oracle_mod()
+    n = m.seq_len(seq)
+    n_cpu = int(os.environ.get("B2_CPU_STEPS", "12"))
+    om = o.OracleModel(path, faithful=True, n_ctx=n + n_cpu + 8)
+    for il in range(cfg.n_layer):
+        k, v = m.kv_read(seq, il, n)
+        om.set_kv(il, k, v)
+    # both sides evaluate the same token at the same position
+    tok = 7
+    g_next, g_logits = m.decode([seq], [tok], want_logits=True)
+    c_logits = om.eval(tok, n)                      # warm-up for the timing as well
+    err = float(np.max(np.abs(g_logits[0] - c_logits)))
+    same = 0
+    g_tok, c_tok = int(g_next[0]), int(np.argmax(c_logits))
+    pos = n + 1
+    cpu_t = 0.0
+    for i in range(n_cpu):
+        same += int(g_tok == c_tok)
+        gl = m.decode([seq], [c_tok], want_logits=True)    # teacher-forced on the CPU token
+        t1 = time.perf_counter()
+        cl = om.eval(c_tok, pos)
+        cpu_t += time.perf_counter() - t1
+        pos += 1
+        err = max(err, float(np.max(np.abs(gl[1][0] - cl))))
+        g_tok, c_tok = int(gl[0][0]), int(np.argmax(cl))
+    v = n_cpu / cpu_t
+    base = {"value": v, "unit": UNIT, "cores": o.lib().ref_num_threads(), "kind": "port",
+            "sample": f"{n_cpu} decode steps at ctx {n}+ continuing the GPU's sequence (KV cache copied from HBM)"}
+    parity = {"logits_max_abs_err": err, "tolerance": 2e-2, "greedy_tokens_equal": f"{same}/{n_cpu}"}
+    return base, parity
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="llama2-7b")
+    ap.add_argument("--ctx", type=int, default=512)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,20 @@
+#!/bin/bash
+# Builds ollama-operator_b200/libb200gguf.so for sm_100a, in-tree (the .so travels to the GPU box).
+set -euo pipefail
+cd "$(dirname "$0")/ollama-operator_b200/csrc"
+OUT=../libb200gguf.so
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function
+       --fmad=true -Xptxas -v -ccbin /usr/bin/g++)
+mkdir -p ../build
+objs=()
+for f in dequant.cu gemv.cu attn.cu step.cu engine.cu api.cu gguf.cpp; do
+  o=../build/${f%.*}.o
+  if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ -n "$(find . ../../include -newer "$o" \( -name '*.h' -o -name '*.cuh' \) -print -quit)" ]; then
+    echo "nvcc $f" >&2
+    "$NVCC" "${FLAGS[@]}" -x cu -c "$f" -o "$o" 2> "../build/${f%.*}.log" || { cat "../build/${f%.*}.log" >&2; exit 1; }
+  fi
+  objs+=("$o")
+done
+"$NVCC" -shared -o "$OUT" "${objs[@]}" -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -lcudart_static -lrt -lpthread -ldl
+echo "built $(readlink -f $OUT)" >&2

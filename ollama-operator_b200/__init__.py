@@ -5,6 +5,6 @@ decode loop of the server container every `Model` CR deploys (reference
 pkg/model/pod.go:14-66).  The compute lives in csrc/ (hand-written sm_100a CUDA behind
 `include/b2gguf.h`); this package only binds it.
 """
-from . import synth  # noqa: F401
+from . import engine, synth  # noqa: F401
 
-__all__ = ["synth"]
+__all__ = ["engine", "synth"]

@@ -1,0 +1,642 @@
+// engine.cu -- model residency, paged KV cache, sequence slots and the decode-step schedule.
+//
+// This is the part of the `ollama serve` process (the container of reference
+// pkg/model/pod.go:14-66) that sits between the HTTP handlers and the kernels: llama.cpp's
+// llama_decode over build_llama / build_phi2 graphs [upstream], rebuilt around CUDA graphs:
+// one decode step is a fixed chain of ~5 kernels per layer (fused norm+QKV+RoPE+KV-append,
+// cluster attention, wo+residual, norm+gate/up+SiLU, down+residual), captured once per
+// sequence slot and replayed; token feedback, position and RoPE table stay on the device.
+#include "engine.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+namespace b2 {
+
+// ---- error state ----------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---- device arena -----------------------------------------------------------------------------
+int Arena::reserve(size_t bytes) {
+    B2_CUDA(cudaMalloc(&base, bytes));
+    cap = bytes; used = 0;
+    return B2_OK;
+}
+void* Arena::take(size_t bytes) {
+    const size_t off = align_up(used, 256);
+    if (off + bytes > cap) return nullptr;
+    used = off + bytes;
+    return (uint8_t*)base + off;
+}
+void Arena::release() {
+    if (base) cudaFree(base);
+    base = nullptr; cap = used = 0;
+}
+
+static size_t qmat_arena_bytes(int type, int64_t rows, int64_t k) {
+    QMat m;
+    qmat_shape(m, type, rows, k);
+    size_t s = 0;
+    for (int p = 0; p < m.n_planes; p++) s += align_up((size_t)rows * m.stride[p], 256);
+    return s + 256;
+}
+static int qmat_alloc(Arena& ar, QMat& m, int type, int64_t rows, int64_t k) {
+    qmat_shape(m, type, rows, k);
+    for (int p = 0; p < m.n_planes; p++) {
+        m.plane[p] = (uint8_t*)ar.take((size_t)rows * m.stride[p]);
+        if (!m.plane[p]) B2_FAIL(B2_ERR_NOMEM, "weight arena exhausted");
+    }
+    return B2_OK;
+}
+
+// ---- Model ---------------------------------------------------------------------------------------
+Model::~Model() {
+    for (auto& s : slots) {
+        if (s.g_full) cudaGraphExecDestroy(s.g_full);
+        if (s.g_nohead) cudaGraphExecDestroy(s.g_nohead);
+    }
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    if (stream) cudaStreamDestroy(stream);
+    if (staging) cudaFree(staging);
+    if (kv_k) cudaFree(kv_k);
+    if (kv_v) cudaFree(kv_v);
+    if (slot_mem) cudaFree(slot_mem);
+    arena.release();
+}
+
+struct TensorPlan { const GgufTensor* t; int64_t rows, k; };
+
+static int need(const GgufFile& f, const std::string& name, int64_t rows, int64_t k, TensorPlan* out, bool quant_ok = true) {
+    const GgufTensor* t = f.find(name);
+    if (!t) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s missing", name.c_str());
+    const int64_t tk = t->ne.size() >= 1 ? t->ne[0] : 0, tr = t->ne.size() >= 2 ? t->ne[1] : 1;
+    if (tk != k || tr != rows) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s has shape [%lld x %lld], expected [%lld x %lld]", name.c_str(),
+                                       (long long)tr, (long long)tk, (long long)rows, (long long)k);
+    if (quant_ok ? !type_is_quant(t->type) : t->type != T_F32)
+        B2_FAIL(B2_ERR_UNSUPPORTED, "gguf: tensor %s has ggml type %d (%s expected)", name.c_str(), t->type,
+                quant_ok ? "Q4_0/Q8_0/Q4_K/Q6_K" : "F32");
+    out->t = t; out->rows = rows; out->k = k;
+    return B2_OK;
+}
+
+// upload one file tensor into the staging buffer and repack it into `dst`
+int Model::upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step,
+                        int64_t src_row0) {
+    const size_t rb = type_row_bytes(t->type, k);
+    B2_CUDA(cudaMemcpyAsync(staging, t->data + (size_t)src_row0 * rb, (size_t)rows * rb, cudaMemcpyHostToDevice, stream));
+    B2_TRY(repack(t->type, staging, rows, k, dst, dst_row0, dst_row_step, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));     // staging is reused by the next tensor
+    return B2_OK;
+}
+int Model::upload_f32(const GgufFile& f, const std::string& name, int64_t n, float** out, bool optional) {
+    const GgufTensor* t = f.find(name);
+    *out = nullptr;
+    if (!t) {
+        if (optional) return B2_OK;
+        B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s missing", name.c_str());
+    }
+    int64_t tn = 1;
+    for (int64_t d : t->ne) tn *= d;
+    if (t->type != T_F32 || tn != n) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s must be F32 with %lld elements", name.c_str(), (long long)n);
+    float* d = (float*)arena.take((size_t)n * 4);
+    if (!d) B2_FAIL(B2_ERR_NOMEM, "weight arena exhausted");
+    B2_CUDA(cudaMemcpy(d, t->data, (size_t)n * 4, cudaMemcpyHostToDevice));
+    *out = d;
+    return B2_OK;
+}
+
+// NeoX rope pairs element p with p + n_rot/2.  The loader stores the rows of every q/k/v head so
+// that partners are adjacent (stored 2p <- p, 2p+1 <- p + n_rot/2), which lets the GEMV
+// epilogue rotate a pair held by one thread; see EPI_QKV_ROPE in gemv.cu.
+int Model::upload_rows_headwise(const GgufTensor* t, int64_t n_heads, int64_t k, const QMat& dst, int64_t dst_row0, int64_t src_row0) {
+    const int hd = hp.head_dim, nr = hp.n_rot;
+    if (!neox) return upload_quant(t, n_heads * hd, k, dst, dst_row0, 1, src_row0);
+    for (int64_t h = 0; h < n_heads; h++) {
+        const int64_t s = src_row0 + h * hd, d = dst_row0 + h * hd;
+        B2_TRY(upload_quant(t, nr / 2, k, dst, d, 2, s));
+        B2_TRY(upload_quant(t, nr / 2, k, dst, d + 1, 2, s + nr / 2));
+        if (hd > nr) B2_TRY(upload_quant(t, hd - nr, k, dst, d + nr, 1, s + nr));
+    }
+    return B2_OK;
+}
+
+int Model::load(const char* path, const b2_load_opts* o) {
+    GgufFile f;
+    B2_TRY(f.open(path));
+    std::string arch;
+    if (!f.get_str("general.architecture", &arch)) B2_FAIL(B2_ERR_FORMAT, "gguf: general.architecture missing");
+    if (arch == "llama") hp.arch = 0;
+    else if (arch == "phi2") hp.arch = 1;
+    else B2_FAIL(B2_ERR_UNSUPPORTED, "architecture '%s' not supported (llama, phi2)", arch.c_str());
+    neox = hp.arch == 1;
+    auto u = [&](const char* key, int* dst, bool required, int dflt) -> int {
+        uint64_t v;
+        if (f.get_u64(arch + "." + key, &v)) { *dst = (int)v; return B2_OK; }
+        if (required) B2_FAIL(B2_ERR_FORMAT, "gguf: key %s.%s missing", arch.c_str(), key);
+        *dst = dflt;
+        return B2_OK;
+    };
+    B2_TRY(u("block_count", &hp.n_layer, true, 0));
+    B2_TRY(u("embedding_length", &hp.n_embd, true, 0));
+    B2_TRY(u("feed_forward_length", &hp.n_ff, true, 0));
+    B2_TRY(u("attention.head_count", &hp.n_head, true, 0));
+    B2_TRY(u("attention.head_count_kv", &hp.n_head_kv, false, 0));
+    B2_TRY(u("context_length", &hp.n_ctx, false, 2048));
+    if (hp.n_head_kv <= 0) hp.n_head_kv = hp.n_head;
+    if (hp.n_layer <= 0 || hp.n_embd <= 0 || hp.n_head <= 0 || hp.n_ff <= 0 || hp.n_embd % hp.n_head)
+        B2_FAIL(B2_ERR_FORMAT, "gguf: implausible hyper-parameters");
+    hp.head_dim = hp.n_embd / hp.n_head;
+    B2_TRY(u("rope.dimension_count", &hp.n_rot, false, hp.head_dim));
+    if (hp.n_rot <= 0 || hp.n_rot > hp.head_dim || (hp.n_rot & 1) || (hp.head_dim & 1)) B2_FAIL(B2_ERR_UNSUPPORTED, "rope dimension count %d", hp.n_rot);
+    double d;
+    hp.norm_eps = 1e-5f;
+    if (f.get_f64(arch + ".attention.layer_norm_rms_epsilon", &d) || f.get_f64(arch + ".attention.layer_norm_epsilon", &d)) hp.norm_eps = (float)d;
+    hp.rope_freq_base = 10000.f;
+    if (f.get_f64(arch + ".rope.freq_base", &d)) hp.rope_freq_base = (float)d;
+    const GgufTensor* te = f.find("token_embd.weight");
+    if (!te || te->ne.size() != 2 || te->ne[0] != hp.n_embd) B2_FAIL(B2_ERR_FORMAT, "gguf: token_embd.weight missing or mis-shaped");
+    hp.n_vocab = (int)te->ne[1];
+
+    max_batch = o && o->max_batch > 0 ? o->max_batch : 1;
+    max_ctx = o && o->max_ctx > 0 ? std::min(o->max_ctx, hp.n_ctx) : hp.n_ctx;
+    if (o && o->tp_size > 1) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor parallelism (tp_size=%d) is not built yet", o->tp_size);
+    const int flags = o ? o->flags : 0;
+    use_pdl = !(flags & B2_LOAD_NO_PDL) && !getenv("B2_NO_PDL");
+    use_graph = !(flags & B2_LOAD_NO_GRAPH) && !getenv("B2_NO_GRAPH");
+
+    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd, F = hp.n_ff, V = hp.n_vocab;
+    if ((nq | nkv | F | V | E) & 1) B2_FAIL(B2_ERR_UNSUPPORTED, "odd matrix dimensions are not supported");
+
+    // ---- plan: which file tensors feed which resident matrices ---------------------------------
+    struct LayerPlan { TensorPlan q, k, v, qkv, o, gate, up, down; };
+    std::vector<LayerPlan> lp(hp.n_layer);
+    TensorPlan embd, head;
+    B2_TRY(need(f, "token_embd.weight", V, E, &embd));
+    const bool tied = f.find("output.weight") == nullptr;
+    B2_TRY(need(f, tied ? "token_embd.weight" : "output.weight", V, E, &head));
+    size_t arena_bytes = qmat_arena_bytes(embd.t->type, V, E) + (tied ? 0 : qmat_arena_bytes(head.t->type, V, E));
+    size_t max_raw = std::max(embd.t->bytes, head.t->bytes);
+    size_t f32_bytes = (size_t)(2 * E + V) * 4 + 1024;
+    for (int l = 0; l < hp.n_layer; l++) {
+        const std::string p = "blk." + std::to_string(l) + ".";
+        LayerPlan& L = lp[l];
+        if (hp.arch == 0) {
+            B2_TRY(need(f, p + "attn_q.weight", nq, E, &L.q));
+            B2_TRY(need(f, p + "attn_k.weight", nkv, E, &L.k));
+            B2_TRY(need(f, p + "attn_v.weight", nkv, E, &L.v));
+            B2_TRY(need(f, p + "ffn_gate.weight", F, E, &L.gate));
+            arena_bytes += qmat_arena_bytes(L.q.t->type, nq, E) + qmat_arena_bytes(L.k.t->type, nkv, E) + qmat_arena_bytes(L.v.t->type, nkv, E);
+            arena_bytes += qmat_arena_bytes(L.gate.t->type, 2 * (int64_t)F, E);
+            max_raw = std::max({max_raw, L.q.t->bytes, L.k.t->bytes, L.v.t->bytes, L.gate.t->bytes});
+        } else {
+            B2_TRY(need(f, p + "attn_qkv.weight", nq + 2 * nkv, E, &L.qkv));
+            arena_bytes += qmat_arena_bytes(L.qkv.t->type, nq + 2 * nkv, E);
+            max_raw = std::max(max_raw, L.qkv.t->bytes);
+        }
+        B2_TRY(need(f, p + "attn_output.weight", E, nq, &L.o));
+        B2_TRY(need(f, p + "ffn_up.weight", F, E, &L.up));
+        B2_TRY(need(f, p + "ffn_down.weight", E, F, &L.down));
+        if (hp.arch == 0 && L.gate.t->type != L.up.t->type) B2_FAIL(B2_ERR_UNSUPPORTED, "layer %d: ffn_gate and ffn_up differ in type", l);
+        if (hp.arch == 1) arena_bytes += qmat_arena_bytes(L.up.t->type, F, E);
+        arena_bytes += qmat_arena_bytes(L.o.t->type, E, nq) + qmat_arena_bytes(L.down.t->type, E, F);
+        max_raw = std::max({max_raw, L.o.t->bytes, L.up.t->bytes, L.down.t->bytes});
+        f32_bytes += (size_t)(4 * E + 2 * (nq + 2 * nkv) + 2 * F) * 4 + 4096;
+    }
+    B2_TRY(arena.reserve(arena_bytes + f32_bytes + (1 << 20)));
+    B2_CUDA(cudaMalloc(&staging, max_raw));
+    B2_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    B2_CUDA(cudaEventCreate(&ev0));
+    B2_CUDA(cudaEventCreate(&ev1));
+
+    // ---- upload + repack -------------------------------------------------------------------------
+    B2_TRY(qmat_alloc(arena, w_embd, embd.t->type, V, E));
+    B2_TRY(upload_quant(embd.t, V, E, w_embd, 0, 1, 0));
+    if (tied) w_head = w_embd;
+    else {
+        B2_TRY(qmat_alloc(arena, w_head, head.t->type, V, E));
+        B2_TRY(upload_quant(head.t, V, E, w_head, 0, 1, 0));
+    }
+    B2_TRY(upload_f32(f, "output_norm.weight", E, &out_norm, false));
+    B2_TRY(upload_f32(f, "output_norm.bias", E, &out_norm_b, true));
+    B2_TRY(upload_f32(f, "output.bias", V, &head_b, true));
+    step_weight_bytes = gemv_weight_bytes(w_head) + (size_t)E * 4;
+    layers.resize(hp.n_layer);
+    for (int l = 0; l < hp.n_layer; l++) {
+        const std::string p = "blk." + std::to_string(l) + ".";
+        LayerPlan& P = lp[l];
+        LayerW& L = layers[l];
+        B2_TRY(upload_f32(f, p + "attn_norm.weight", E, &L.attn_norm, false));
+        B2_TRY(upload_f32(f, p + "attn_norm.bias", E, &L.attn_norm_b, true));
+        if (hp.arch == 0) {
+            // q | k | v fused as far as the tensor types allow (Q4_K_M mixes Q4_K q,k with Q6_K v)
+            const TensorPlan* parts[3] = {&P.q, &P.k, &P.v};
+            const int64_t prow[3] = {nq, nkv, nkv};
+            int64_t row0 = 0;
+            for (int i = 0; i < 3;) {
+                int j = i;
+                int64_t rows = 0;
+                while (j < 3 && parts[j]->t->type == parts[i]->t->type) rows += prow[j++];
+                QkvSeg seg;
+                seg.row0 = row0;
+                B2_TRY(qmat_alloc(arena, seg.W, parts[i]->t->type, rows, E));
+                int64_t r = 0;
+                for (int q = i; q < j; q++) {
+                    B2_TRY(upload_rows_headwise(parts[q]->t, prow[q] / hd, E, seg.W, r, 0));
+                    r += prow[q];
+                }
+                L.qkv.push_back(seg);
+                row0 += rows;
+                i = j;
+            }
+            B2_TRY(upload_f32(f, p + "ffn_norm.weight", E, &L.ffn_norm, false));
+            B2_TRY(qmat_alloc(arena, L.w_up, P.gate.t->type, 2 * (int64_t)F, E));      // rows interleaved (gate_i, up_i)
+            B2_TRY(upload_quant(P.gate.t, F, E, L.w_up, 0, 2, 0));
+            B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 1, 2, 0));
+        } else {
+            QkvSeg seg;
+            seg.row0 = 0;
+            B2_TRY(qmat_alloc(arena, seg.W, P.qkv.t->type, nq + 2 * nkv, E));
+            B2_TRY(upload_rows_headwise(P.qkv.t, (nq + 2 * nkv) / hd, E, seg.W, 0, 0));
+            L.qkv.push_back(seg);
+            // bias rows follow the same permutation
+            const GgufTensor* tb = f.find(p + "attn_qkv.bias");
+            if (tb) {
+                if (tb->type != T_F32 || tb->ne.empty() || tb->ne[0] != nq + 2 * nkv) B2_FAIL(B2_ERR_FORMAT, "gguf: %sattn_qkv.bias mis-shaped", p.c_str());
+                std::vector<float> b((size_t)nq + 2 * nkv);
+                const float* src = (const float*)tb->data;
+                for (int64_t h = 0; h < (nq + 2 * nkv) / hd; h++)
+                    for (int e = 0; e < hd; e++) {
+                        const int dsti = e < hp.n_rot / 2 ? 2 * e : e < hp.n_rot ? 2 * (e - hp.n_rot / 2) + 1 : e;
+                        b[h * hd + dsti] = src[h * hd + e];
+                    }
+                L.b_qkv = (float*)arena.take(b.size() * 4);
+                if (!L.b_qkv) B2_FAIL(B2_ERR_NOMEM, "weight arena exhausted");
+                B2_CUDA(cudaMemcpy(L.b_qkv, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
+            }
+            B2_TRY(qmat_alloc(arena, L.w_up, P.up.t->type, F, E));
+            B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 0, 1, 0));
+            B2_TRY(upload_f32(f, p + "ffn_up.bias", F, &L.b_up, true));
+            B2_TRY(upload_f32(f, p + "ffn_down.bias", E, &L.b_down, true));
+            B2_TRY(upload_f32(f, p + "attn_output.bias", E, &L.b_o, true));
+        }
+        B2_TRY(qmat_alloc(arena, L.w_o, P.o.t->type, E, nq));
+        B2_TRY(upload_quant(P.o.t, E, nq, L.w_o, 0, 1, 0));
+        B2_TRY(qmat_alloc(arena, L.w_down, P.down.t->type, E, F));
+        B2_TRY(upload_quant(P.down.t, E, F, L.w_down, 0, 1, 0));
+        for (auto& s : L.qkv) step_weight_bytes += gemv_weight_bytes(s.W);
+        step_weight_bytes += gemv_weight_bytes(L.w_o) + gemv_weight_bytes(L.w_up) + gemv_weight_bytes(L.w_down) + (size_t)2 * E * 4;
+    }
+    weight_bytes = arena.used;
+    cudaFree(staging);
+    staging = nullptr;
+
+    // ---- KV cache pages + slots --------------------------------------------------------------------
+    pages_per_seq = (max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    n_pages = pages_per_seq * max_batch;
+    layer_kv_elems = (size_t)n_pages * PAGE_TOKENS * nkv;
+    B2_CUDA(cudaMalloc(&kv_k, layer_kv_elems * hp.n_layer * sizeof(__half)));
+    B2_CUDA(cudaMalloc(&kv_v, layer_kv_elems * hp.n_layer * sizeof(__half)));
+    B2_CUDA(cudaMemset(kv_k, 0, layer_kv_elems * hp.n_layer * sizeof(__half)));
+    B2_CUDA(cudaMemset(kv_v, 0, layer_kv_elems * hp.n_layer * sizeof(__half)));
+    for (int i = n_pages - 1; i >= 0; i--) free_pages.push_back(i);
+
+    // per-slot device block
+    out_cap = max_ctx;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { const size_t o2 = align_up(off, 256); off = o2 + bytes; return o2; };
+    const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
+                 o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
+                 o_cs = carve((size_t)hp.n_rot / 2 * 8), o_pos = carve(4), o_key = carve(8), o_out = carve((size_t)out_cap * 4),
+                 o_forced = carve((size_t)max_ctx * 4);
+    const size_t slot_bytes = align_up(off, 256);
+    B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
+    B2_CUDA(cudaMemset(slot_mem, 0, slot_bytes * max_batch));
+    slots.resize(max_batch);
+    for (int i = 0; i < max_batch; i++) {
+        uint8_t* b = (uint8_t*)slot_mem + slot_bytes * i;
+        Slot& s = slots[i];
+        s.d_state = (SeqState*)(b + o_state); s.d_page_table = (int*)(b + o_pt); s.x = (float*)(b + o_x); s.q = (float*)(b + o_q);
+        s.att = (float*)(b + o_att); s.att2 = (float*)(b + o_att2); s.h = (float*)(b + o_h); s.logits = (float*)(b + o_logits);
+        s.rope_cs = (float2*)(b + o_cs); s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
+        s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced);
+    }
+    theta_scale = powf(hp.rope_freq_base, -2.0f / hp.n_rot);
+    return B2_OK;
+}
+
+// ---- sequences -------------------------------------------------------------------------------------
+int Model::seq_new(int* out) {
+    for (int i = 0; i < max_batch; i++)
+        if (!slots[i].used) {
+            slots[i].used = true;
+            slots[i].len = 0;
+            slots[i].host = SeqState{};
+            *out = i;
+            return B2_OK;
+        }
+    B2_FAIL(B2_ERR_NOMEM, "all %d sequence slots are in use", max_batch);
+}
+int Model::check_seq(int seq) const {
+    if (seq < 0 || seq >= max_batch || !slots[seq].used) B2_FAIL(B2_ERR_STATE, "sequence %d is not open", seq);
+    return B2_OK;
+}
+int Model::seq_free(int seq) {
+    B2_TRY(check_seq(seq));
+    Slot& s = slots[seq];
+    for (int p : s.pages) free_pages.push_back(p);
+    s.pages.clear();
+    s.used = false;
+    s.len = 0;
+    return B2_OK;
+}
+int Model::seq_truncate(int seq, int n_keep) {
+    B2_TRY(check_seq(seq));
+    Slot& s = slots[seq];
+    if (n_keep < 0 || n_keep > s.len) B2_FAIL(B2_ERR_ARG, "truncate: n_keep=%d outside [0,%d]", n_keep, s.len);
+    s.len = n_keep;
+    const size_t keep_pages = (size_t)(n_keep + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    while (s.pages.size() > keep_pages) { free_pages.push_back(s.pages.back()); s.pages.pop_back(); }
+    return B2_OK;
+}
+// make sure pages exist for positions [0, upto) and the device page table matches
+int Model::ensure_pages(Slot& s, int upto) {
+    if (upto > max_ctx) B2_FAIL(B2_ERR_NOMEM, "sequence would grow to %d tokens, max_ctx is %d", upto, max_ctx);
+    const size_t want = (size_t)(upto + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const size_t had = s.pages.size();
+    while (s.pages.size() < want) {
+        if (free_pages.empty()) B2_FAIL(B2_ERR_NOMEM, "KV cache pages exhausted");
+        s.pages.push_back(free_pages.back());
+        free_pages.pop_back();
+    }
+    if (s.pages.size() != had || !s.table_synced) {
+        B2_CUDA(cudaMemcpyAsync(s.d_page_table, s.pages.data(), s.pages.size() * 4, cudaMemcpyHostToDevice, stream));
+        s.table_synced = true;
+    }
+    return B2_OK;
+}
+
+// ---- one decode step, as a chain of kernel launches on `stream` -----------------------------------
+int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof) {
+    auto mark = [&](int cls) -> int {
+        if (!prof) return B2_OK;
+        cudaEvent_t e;
+        B2_CUDA(cudaEventCreate(&e));
+        B2_CUDA(cudaEventRecord(e, stream));
+        prof->ev.push_back(e);
+        prof->cls.push_back(cls);
+        return B2_OK;
+    };
+    B2_TRY(mark(-1));
+    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd;
+    int nl = 0;
+    const bool pdl = use_pdl;
+    {
+        StepBeginArgs a;
+        a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.rope_cs = s.rope_cs; a.pos_out = s.d_pos; a.argmax_key = s.d_key;
+        a.n_rot = hp.n_rot; a.theta_scale = theta_scale;
+        B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
+    }
+    for (int l = 0; l < hp.n_layer; l++) {
+        const LayerW& L = layers[l];
+        __half* kb = kv_k + layer_kv_elems * l;
+        __half* vb = kv_v + layer_kv_elems * l;
+        for (const QkvSeg& seg : L.qkv) {
+            GemvArgs a;
+            a.W = seg.W; a.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; a.epi = EPI_QKV_ROPE;
+            a.x = s.x; a.gain = L.attn_norm; a.nbias = L.attn_norm_b; a.eps = hp.norm_eps;
+            a.bias = L.b_qkv; a.y = s.q; a.epi_row0 = seg.row0;
+            a.n_q = nq; a.n_kv = nkv; a.head_dim = hd; a.n_rot = hp.n_rot; a.rope_neox = neox ? 1 : 0;
+            a.q_scale = hp.arch == 1 ? 1.0f / sqrtf((float)hd) : 1.0f;
+            a.rope_cs = s.rope_cs;
+            a.kv.k_base = kb; a.kv.v_base = vb; a.kv.page_table = s.d_page_table; a.kv.pos = s.d_pos;
+            a.kv.page_tokens = PAGE_TOKENS; a.kv.kv_dim = nkv;
+            B2_TRY(gemv_launch(a, stream, pdl)); nl++; B2_TRY(mark(1));
+        }
+        {
+            AttnArgs a;
+            a.q = s.q; a.out = s.att; a.k_base = kb; a.v_base = vb; a.page_table = s.d_page_table; a.pos = s.d_pos;
+            a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.head_dim = hd; a.page_tokens = PAGE_TOKENS; a.kv_dim = nkv;
+            a.max_ctx = max_ctx;
+            a.scale = hp.arch == 1 ? 1.0f : 1.0f / sqrtf((float)hd);
+            B2_TRY(attn_decode_launch(a, stream, pdl)); nl++; B2_TRY(mark(2));
+        }
+        if (hp.arch == 0) {
+            GemvArgs o;
+            o.W = L.w_o; o.pro = PRO_PLAIN; o.epi = EPI_RESIDUAL; o.x = s.att; o.y = s.x;
+            B2_TRY(gemv_launch(o, stream, pdl)); nl++; B2_TRY(mark(3));
+            GemvArgs u;
+            u.W = L.w_up; u.pro = PRO_RMSNORM; u.epi = EPI_SILU_MUL; u.x = s.x; u.gain = L.ffn_norm; u.eps = hp.norm_eps; u.y = s.h;
+            B2_TRY(gemv_launch(u, stream, pdl)); nl++; B2_TRY(mark(4));
+            GemvArgs d;
+            d.W = L.w_down; d.pro = PRO_PLAIN; d.epi = EPI_RESIDUAL; d.x = s.h; d.y = s.x;
+            B2_TRY(gemv_launch(d, stream, pdl)); nl++; B2_TRY(mark(5));
+        } else {
+            GemvArgs o;
+            o.W = L.w_o; o.pro = PRO_PLAIN; o.epi = EPI_STORE; o.x = s.att; o.bias = L.b_o; o.y = s.att2;
+            B2_TRY(gemv_launch(o, stream, pdl)); nl++; B2_TRY(mark(3));
+            GemvArgs u;
+            u.W = L.w_up; u.pro = PRO_LAYERNORM; u.epi = EPI_GELU; u.x = s.x; u.gain = L.attn_norm; u.nbias = L.attn_norm_b;
+            u.eps = hp.norm_eps; u.bias = L.b_up; u.y = s.h;
+            B2_TRY(gemv_launch(u, stream, pdl)); nl++; B2_TRY(mark(4));
+            GemvArgs d;
+            d.W = L.w_down; d.pro = PRO_PLAIN; d.epi = EPI_RESIDUAL2; d.x = s.h; d.bias = L.b_down; d.y = s.x; d.y2 = s.att2;
+            B2_TRY(gemv_launch(d, stream, pdl)); nl++; B2_TRY(mark(5));
+        }
+    }
+    if (with_head) {
+        GemvArgs h;
+        h.W = w_head; h.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; h.epi = EPI_LOGITS;
+        h.x = s.x; h.gain = out_norm; h.nbias = out_norm_b; h.eps = hp.norm_eps; h.bias = head_b; h.y = s.logits; h.argmax_key = s.d_key;
+        B2_TRY(gemv_launch(h, stream, pdl)); nl++; B2_TRY(mark(6));
+    }
+    {
+        StepEndArgs a;
+        a.st = s.d_state; a.argmax_key = s.d_key; a.forced = s.d_forced; a.out_toks = s.d_out; a.out_cap = out_cap; a.use_argmax = with_head ? 1 : 0;
+        B2_TRY(step_end_launch(a, stream, pdl)); nl++; B2_TRY(mark(7));
+    }
+    *n_launch = nl;
+    return B2_OK;
+}
+
+// Run `n` steps of one kind.  The first step of each kind runs eagerly (it also sets the
+// kernels' shared-memory attributes); after that a captured graph of the step is replayed.
+int Model::run_steps(Slot& s, bool with_head, int n) {
+    cudaGraphExec_t& g = with_head ? s.g_full : s.g_nohead;
+    int& gl = with_head ? s.gl_full : s.gl_nohead;
+    bool& warmed = with_head ? s.warm_full : s.warm_nohead;
+    for (int i = 0; i < n; i++) {
+        if (!use_graph || !warmed) {
+            int nl = 0;
+            B2_TRY(enqueue_step(s, with_head, &nl, nullptr));
+            warmed = true;
+            gl = nl;
+            launches += nl; last_launches += nl;
+            continue;
+        }
+        if (!g) {
+            cudaGraph_t graph = nullptr;
+            B2_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+            int nl = 0;
+            const int rc = enqueue_step(s, with_head, &nl, nullptr);
+            cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+            if (rc != B2_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+            if (ce == cudaSuccess) ce = cudaGraphInstantiate(&g, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (ce != cudaSuccess) {
+                g = nullptr;
+                cudaGetLastError();
+                if (use_pdl) { use_pdl = false; i--; continue; }     // retry the capture without PDL edges
+                B2_FAIL(B2_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(ce));
+            }
+            gl = nl;
+        }
+        B2_CUDA(cudaGraphLaunch(g, stream));
+        launches += gl; last_launches += gl;
+    }
+    steps += n; last_steps += n;
+    return B2_OK;
+}
+
+int Model::begin_call() {
+    last_steps = 0; last_launches = 0;
+    B2_CUDA(cudaEventRecord(ev0, stream));
+    return B2_OK;
+}
+int Model::end_call(Slot* s) {
+    B2_CUDA(cudaEventRecord(ev1, stream));
+    if (s) B2_CUDA(cudaMemcpyAsync(&s->host, s->d_state, sizeof(SeqState), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0;
+    B2_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    last_ms = ms;
+    return B2_OK;
+}
+
+int Model::prefill(int seq, const int32_t* toks, int n, float* logits) {
+    B2_TRY(check_seq(seq));
+    if (!toks || n <= 0) B2_FAIL(B2_ERR_ARG, "prefill: need at least one token");
+    for (int i = 0; i < n; i++)
+        if (toks[i] < 0 || toks[i] >= hp.n_vocab) B2_FAIL(B2_ERR_ARG, "prefill: token %d at %d outside the vocabulary [0,%d)", toks[i], i, hp.n_vocab);
+    Slot& s = slots[seq];
+    B2_TRY(ensure_pages(s, s.len + n));
+    B2_TRY(begin_call());
+    // The prompt is walked with the decode kernels, one token per step (a GEMM-shaped prefill
+    // is the next milestone); prompt tokens are forced from the device-side list.
+    SeqState st{};
+    st.pos = s.len; st.cur_tok = toks[0]; st.n_forced = n - 1; st.forced_idx = 0; st.n_out = 0;
+    B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
+    if (n > 1) B2_CUDA(cudaMemcpyAsync(s.d_forced, toks + 1, (size_t)(n - 1) * 4, cudaMemcpyHostToDevice, stream));
+    if (n > 1) B2_TRY(run_steps(s, false, n - 1));
+    B2_TRY(run_steps(s, true, 1));
+    if (logits) B2_CUDA(cudaMemcpyAsync(logits, s.logits, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
+    B2_TRY(end_call(&s));
+    s.len += n;
+    return B2_OK;
+}
+
+int Model::decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* next_tok, float* logits) {
+    if (n_seq <= 0 || !seqs || !last_tok) B2_FAIL(B2_ERR_ARG, "decode: bad arguments");
+    for (int i = 0; i < n_seq; i++) {
+        B2_TRY(check_seq(seqs[i]));
+        if (last_tok[i] < 0 || last_tok[i] >= hp.n_vocab) B2_FAIL(B2_ERR_ARG, "decode: token %d outside the vocabulary", last_tok[i]);
+        for (int j = 0; j < i; j++) if (seqs[j] == seqs[i]) B2_FAIL(B2_ERR_ARG, "decode: sequence %d listed twice", seqs[i]);
+        B2_TRY(ensure_pages(slots[seqs[i]], slots[seqs[i]].len + 1));
+    }
+    B2_TRY(begin_call());
+    for (int i = 0; i < n_seq; i++) {
+        Slot& s = slots[seqs[i]];
+        SeqState st{};
+        st.pos = s.len; st.cur_tok = last_tok[i];
+        B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
+        B2_TRY(run_steps(s, true, 1));
+        if (logits) B2_CUDA(cudaMemcpyAsync(logits + (size_t)i * hp.n_vocab, s.logits, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
+        B2_CUDA(cudaMemcpyAsync(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost, stream));
+    }
+    B2_TRY(end_call(nullptr));
+    for (int i = 0; i < n_seq; i++) {
+        Slot& s = slots[seqs[i]];
+        s.len += 1;
+        if (next_tok) next_tok[i] = s.host.cur_tok;
+    }
+    return B2_OK;
+}
+
+int Model::decode_greedy(int seq, int32_t first_tok, int n_steps, int32_t* out_toks) {
+    B2_TRY(check_seq(seq));
+    if (n_steps <= 0 || n_steps > out_cap) B2_FAIL(B2_ERR_ARG, "decode_greedy: n_steps=%d outside [1,%d]", n_steps, out_cap);
+    Slot& s = slots[seq];
+    if (first_tok >= hp.n_vocab) B2_FAIL(B2_ERR_ARG, "decode_greedy: token %d outside the vocabulary", first_tok);
+    if (first_tok < 0 && s.len == 0) B2_FAIL(B2_ERR_STATE, "decode_greedy: nothing to continue from");
+    B2_TRY(ensure_pages(s, s.len + n_steps));
+    B2_TRY(begin_call());
+    SeqState st{};
+    st.pos = s.len; st.cur_tok = first_tok >= 0 ? first_tok : s.host.cur_tok;
+    B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
+    B2_TRY(run_steps(s, true, n_steps));
+    if (out_toks) B2_CUDA(cudaMemcpyAsync(out_toks, s.d_out, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, stream));
+    B2_TRY(end_call(&s));
+    s.len += n_steps;
+    return B2_OK;
+}
+
+// One eager decode step with a CUDA event after every launch: per-kernel-class device time
+// inside a real step (no PDL overlap, so the classes add up to a slightly longer step).
+int Model::profile_step(int seq, int32_t tok, float* class_ms, int* class_launches) {
+    B2_TRY(check_seq(seq));
+    if (tok < 0 || tok >= hp.n_vocab || !class_ms || !class_launches) B2_FAIL(B2_ERR_ARG, "profile_step: bad arguments");
+    Slot& s = slots[seq];
+    B2_TRY(ensure_pages(s, s.len + 1));
+    SeqState st{};
+    st.pos = s.len; st.cur_tok = tok;
+    B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
+    StepProfile prof;
+    int nl = 0;
+    const bool saved = use_pdl;
+    use_pdl = false;
+    const int rc = enqueue_step(s, true, &nl, &prof);
+    use_pdl = saved;
+    cudaStreamSynchronize(stream);
+    for (int i = 0; i < 8; i++) { class_ms[i] = 0.f; class_launches[i] = 0; }
+    if (rc == B2_OK)
+        for (size_t i = 1; i < prof.ev.size(); i++) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, prof.ev[i - 1], prof.ev[i]);
+            class_ms[prof.cls[i]] += ms;
+            class_launches[prof.cls[i]]++;
+        }
+    for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
+    B2_TRY(rc);
+    B2_CUDA(cudaMemcpy(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost));
+    s.len += 1; steps += 1; launches += nl;
+    return B2_OK;
+}
+
+int Model::kv_read(int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok) {
+    B2_TRY(check_seq(seq));
+    Slot& s = slots[seq];
+    if (layer < 0 || layer >= hp.n_layer || n_tok < 0 || n_tok > s.len) B2_FAIL(B2_ERR_ARG, "kv_read: layer %d / n_tok %d out of range", layer, n_tok);
+    const size_t nkv = (size_t)hp.n_head_kv * hp.head_dim;
+    for (int t0 = 0; t0 < n_tok; t0 += PAGE_TOKENS) {
+        const int cnt = std::min(PAGE_TOKENS, n_tok - t0);
+        const size_t src = ((size_t)s.pages[t0 / PAGE_TOKENS] * PAGE_TOKENS) * nkv + layer_kv_elems * layer;
+        if (k_out) B2_CUDA(cudaMemcpy(k_out + (size_t)t0 * nkv, kv_k + src, cnt * nkv * 2, cudaMemcpyDeviceToHost));
+        if (v_out) B2_CUDA(cudaMemcpy(v_out + (size_t)t0 * nkv, kv_v + src, cnt * nkv * 2, cudaMemcpyDeviceToHost));
+    }
+    return B2_OK;
+}
+
+}  // namespace b2

@@ -1,0 +1,103 @@
+// engine.h -- host-side model / sequence state behind the C ABI.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/b2gguf.h"
+#include "common.cuh"
+#include "formats.cuh"
+#include "gguf.h"
+#include "kernels.h"
+
+namespace b2 {
+
+constexpr int PAGE_TOKENS = 64;    // tokens per KV-cache page
+
+struct Arena {                     // one cudaMalloc that all resident weights are carved from
+    void* base = nullptr;
+    size_t cap = 0, used = 0;
+    int reserve(size_t bytes);
+    void* take(size_t bytes);
+    void release();
+};
+
+struct HParams {
+    int arch = 0;                  // 0 llama, 1 phi2
+    int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx = 0, n_rot = 0;
+    float norm_eps = 1e-5f, rope_freq_base = 10000.f;
+};
+
+struct QkvSeg { QMat W; int64_t row0 = 0; };     // a run of q|k|v rows that share a tensor type
+
+struct LayerW {
+    std::vector<QkvSeg> qkv;
+    QMat w_o, w_up, w_down;        // llama: w_up holds gate and up interleaved row by row
+    float *attn_norm = nullptr, *attn_norm_b = nullptr, *ffn_norm = nullptr;
+    float *b_qkv = nullptr, *b_o = nullptr, *b_up = nullptr, *b_down = nullptr;
+};
+
+struct Slot {
+    bool used = false;
+    int len = 0;                   // tokens in the KV cache
+    std::vector<int> pages;        // physical pages, in logical order
+    bool table_synced = false;
+    SeqState host{};               // mirror of the device state after the last call
+    SeqState* d_state = nullptr;
+    int* d_page_table = nullptr;
+    float *x = nullptr, *q = nullptr, *att = nullptr, *att2 = nullptr, *h = nullptr, *logits = nullptr;
+    float2* rope_cs = nullptr;
+    int* d_pos = nullptr;
+    unsigned long long* d_key = nullptr;
+    int *d_out = nullptr, *d_forced = nullptr;
+    cudaGraphExec_t g_full = nullptr, g_nohead = nullptr;
+    int gl_full = 0, gl_nohead = 0;
+    bool warm_full = false, warm_nohead = false;
+};
+
+struct StepProfile { std::vector<cudaEvent_t> ev; std::vector<int> cls; };
+
+struct Model {
+    HParams hp;
+    bool neox = false, use_pdl = true, use_graph = true;
+    int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
+    float theta_scale = 0.f;
+    Arena arena;
+    void* staging = nullptr;
+    QMat w_embd, w_head;
+    float *out_norm = nullptr, *out_norm_b = nullptr, *head_b = nullptr;
+    std::vector<LayerW> layers;
+    __half *kv_k = nullptr, *kv_v = nullptr;
+    size_t layer_kv_elems = 0;
+    std::vector<int> free_pages;
+    void* slot_mem = nullptr;
+    std::vector<Slot> slots;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    size_t weight_bytes = 0, step_weight_bytes = 0;
+    uint64_t steps = 0, launches = 0, last_steps = 0, last_launches = 0;
+    double last_ms = 0;
+
+    ~Model();
+    int load(const char* path, const b2_load_opts* o);
+    int seq_new(int* out);
+    int seq_free(int seq);
+    int seq_truncate(int seq, int n_keep);
+    int check_seq(int seq) const;
+    int prefill(int seq, const int32_t* toks, int n, float* logits);
+    int decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* next_tok, float* logits);
+    int decode_greedy(int seq, int32_t first_tok, int n_steps, int32_t* out_toks);
+    int kv_read(int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok);
+    int profile_step(int seq, int32_t tok, float* class_ms, int* class_launches);
+
+  private:
+    int upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step, int64_t src_row0);
+    int upload_f32(const GgufFile& f, const std::string& name, int64_t n, float** out, bool optional);
+    int upload_rows_headwise(const GgufTensor* t, int64_t n_heads, int64_t k, const QMat& dst, int64_t dst_row0, int64_t src_row0);
+    int ensure_pages(Slot& s, int upto);
+    int enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof);
+    int run_steps(Slot& s, bool with_head, int n);
+    int begin_call();
+    int end_call(Slot* s);
+};
+
+}  // namespace b2

@@ -1,0 +1,106 @@
+// kernels.h -- internal interface between the engine (host C++) and the CUDA kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "formats.cuh"
+
+namespace b2 {
+
+// ---- dequant.cu ---------------------------------------------------------------------------
+int dequant_raw(int type, const void* d_blocks, int64_t n_elem, float* d_out, cudaStream_t st);
+int repack(int type, const void* d_raw, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step,
+           cudaStream_t st);
+int dequant_rows(const QMat& m, int64_t row0, int64_t nrows, float* d_out, cudaStream_t st);
+
+// ---- gemv.cu: y = epilogue(W . quantise(prologue(x))) for one activation vector --------------
+enum GemvPro : int { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_LAYERNORM = 2 };
+enum GemvEpi : int {
+    EPI_STORE = 0,       // y[r] = v
+    EPI_RESIDUAL = 1,    // y[r] += v            (y is the residual stream, updated in place)
+    EPI_SILU_MUL = 2,    // rows interleaved (gate_i, up_i): y[i] = silu(v[2i]) * v[2i+1]
+    EPI_QKV_ROPE = 3,    // rows [q | k | v]: rope on q,k; q -> y (f32), k,v -> f16 KV cache page
+    EPI_LOGITS = 4,      // y[r] = v and a running arg-max into *argmax_key
+    EPI_GELU = 5,        // y[r] = gelu(v)
+    EPI_RESIDUAL2 = 6,   // y[r] = (v + y2[r]) + y[r]   (phi-2 parallel block: ffn + attn + x)
+};
+
+struct KvDesc {                 // where the new token's K and V go (one layer, one sequence slot)
+    __half* k_base = nullptr;   // [n_pages][page_tokens][kv_dim]
+    __half* v_base = nullptr;
+    const int* page_table = nullptr;   // logical page -> physical page, for this slot
+    const int* pos = nullptr;          // device scalar: position of the token being decoded
+    int page_tokens = 0, kv_dim = 0;
+};
+
+struct GemvArgs {
+    QMat W;
+    int pro = PRO_PLAIN, epi = EPI_STORE;
+    const float* x = nullptr;      // [K]
+    const float* gain = nullptr;   // [K]  norm gain
+    const float* nbias = nullptr;  // [K]  layer-norm bias
+    float eps = 0.f;
+    const float* bias = nullptr;   // [rows] optional, added before the epilogue
+    float* y = nullptr;
+    const float* y2 = nullptr;
+    int64_t epi_row0 = 0;          // added to the matrix row before the epilogue (split QKV matrices)
+    // EPI_QKV_ROPE
+    int n_q = 0, n_kv = 0, head_dim = 0, n_rot = 0, rope_neox = 0;
+    float q_scale = 1.f;
+    const float2* rope_cs = nullptr;   // [n_rot/2] (cos, sin) at the current position
+    KvDesc kv;
+    // EPI_LOGITS
+    unsigned long long* argmax_key = nullptr;
+};
+
+struct GemvTune { int nb = 0, g = 0, rpg = 0, ns = 0, ctas_per_sm = 0; };  // 0 = heuristic
+
+int gemv_launch(const GemvArgs& a, cudaStream_t st, bool pdl, const GemvTune* tune = nullptr);
+// bytes of weight data one launch streams (the algorithmic bytes of the kernel)
+size_t gemv_weight_bytes(const QMat& W);
+
+// ---- attn.cu: flash-decode over the paged f16 KV cache ---------------------------------------
+struct AttnArgs {
+    const float* q = nullptr;          // [n_head][head_dim] f32 (rounded to f16 inside, as ggml does)
+    float* out = nullptr;              // [n_head][head_dim] f32
+    const __half* k_base = nullptr;    // [n_pages][page_tokens][kv_dim]
+    const __half* v_base = nullptr;
+    const int* page_table = nullptr;
+    const int* pos = nullptr;          // attends to cache rows [0, *pos]
+    int n_head = 0, n_head_kv = 0, head_dim = 0, page_tokens = 0, kv_dim = 0;
+    int max_ctx = 0;                   // upper bound of *pos + 1 (sizes the score buffer)
+    float scale = 1.f;
+};
+int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster = 0);
+
+// ---- step.cu: per-step bookkeeping kernels ----------------------------------------------------
+struct SeqState {        // one per sequence slot, resident on the device
+    int pos;             // position of the token about to be evaluated
+    int cur_tok;         // that token
+    int n_forced;        // tokens still to be taken from `forced` (prompt) instead of arg-max
+    int forced_idx;
+    int n_out;           // tokens emitted into out_toks so far
+    int pad[3];
+};
+struct StepBeginArgs {
+    SeqState* st = nullptr;
+    QMat embd;
+    float* x = nullptr;            // [n_embd]
+    float2* rope_cs = nullptr;     // [n_rot/2]
+    int* pos_out = nullptr;        // device scalar consumed by the layer kernels
+    unsigned long long* argmax_key = nullptr;
+    int n_rot = 0;
+    float theta_scale = 0.f;       // freq_base^(-2/n_rot)
+};
+int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
+struct StepEndArgs {
+    SeqState* st = nullptr;
+    const unsigned long long* argmax_key = nullptr;
+    const int* forced = nullptr;   // prompt tokens
+    int* out_toks = nullptr;       // ring of emitted tokens
+    int out_cap = 0;
+    int use_argmax = 1;            // 0: prompt step, the head did not run
+};
+int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl);
+
+}  // namespace b2

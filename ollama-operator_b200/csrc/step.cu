@@ -1,0 +1,83 @@
+// step.cu -- the two small bookkeeping kernels that bracket a decode step.  They keep the whole
+// greedy loop on the device (token feedback, position, RoPE table), so a CUDA graph of one step
+// can be replayed back to back with no host round trip.
+#include <math.h>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "qmat_dev.cuh"
+
+namespace b2 {
+
+// step_begin: x = embedding row of the current token (ggml get_rows), RoPE (cos, sin) table for
+// the current position, position scalar for the layer kernels, arg-max accumulator cleared.
+__global__ void step_begin_kernel(const StepBeginArgs a) {
+    pdl_trigger();
+    pdl_wait();
+    const int tok = a.st->cur_tok, pos = a.st->pos;
+    const int E = (int)a.embd.k;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < E; i += gridDim.x * blockDim.x) a.x[i] = qmat_elem(a.embd, tok, i);
+    if (blockIdx.x == 0) {
+        // ggml rope: theta starts at pos and is multiplied by theta_scale once per pair
+        for (int p = threadIdx.x; p < a.n_rot / 2; p += blockDim.x) {
+            float theta = (float)pos;
+            for (int k = 0; k < p; k++) theta = __fmul_rn(theta, a.theta_scale);
+            a.rope_cs[p] = make_float2(cosf(theta), sinf(theta));
+        }
+        if (threadIdx.x == 0) {
+            *a.pos_out = pos;
+            *a.argmax_key = 0ull;
+        }
+    }
+}
+
+int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    const int E = (int)a.embd.k;
+    cfg.gridDim = dim3((E + 255) / 256);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, step_begin_kernel, a));
+    return B2_OK;
+}
+
+// step_end: pick the next token (prompt token while any are left, else the arg-max of the
+// logits), record it, advance the position.
+__global__ void step_end_kernel(const StepEndArgs a) {
+    pdl_trigger();
+    pdl_wait();
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    SeqState* s = a.st;
+    int next;
+    if (s->forced_idx < s->n_forced) {
+        next = a.forced[s->forced_idx++];
+    } else {
+        const unsigned long long key = a.use_argmax ? *a.argmax_key : 0ull;
+        next = (int)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+        if (a.out_toks && s->n_out < a.out_cap) a.out_toks[s->n_out] = next;
+        s->n_out++;
+    }
+    s->cur_tok = next;
+    s->pos++;
+}
+
+int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1);
+    cfg.blockDim = dim3(32);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, step_end_kernel, a));
+    return B2_OK;
+}
+
+}  // namespace b2

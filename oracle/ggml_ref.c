@@ -290,49 +290,52 @@ void ref_make_q6_K(const float *x, void *vy, int64_t k) {
 
 /* ---- dot products ------------------------------------------------------------------ */
 /* The integer part of every block dot is exact whatever the evaluation order, so the
- * AVX2 helper below only accelerates it; the float accumulation keeps the order of
- * ggml's generic C path: sumf += sumi * d_w * d_a, block after block. */
-#if defined(__x86_64__)
+ * AVX2 helper below (compiled in by `make SIMD=1`) only accelerates it; the float
+ * accumulation keeps the order of ggml's generic C path. */
+#if defined(__x86_64__) && defined(REF_SIMD)
 #include <immintrin.h>
-__attribute__((target("avx2"))) static inline int q4_0_q8_0_sumi_avx2(const blk_q4_0 *x, const blk_q8_0 *y) {
+/* eight int32 partial sums of one block: sum over the vector == the block's sumi */
+static inline __m256i q4_0_q8_0_p32(const blk_q4_0 *x, const blk_q8_0 *y) {
     const __m128i raw = _mm_loadu_si128((const __m128i *)x->qs);
     const __m256i nib = _mm256_and_si256(_mm256_set_m128i(_mm_srli_epi16(raw, 4), raw), _mm256_set1_epi8(0x0F));
     const __m256i w = _mm256_sub_epi8(nib, _mm256_set1_epi8(8));
     const __m256i a = _mm256_loadu_si256((const __m256i *)y->qs);
-    const __m256i aw = _mm256_sign_epi8(w, w);          /* |w| */
-    const __m256i sa = _mm256_sign_epi8(a, w);          /* a * sign(w) */
-    const __m256i p16 = _mm256_maddubs_epi16(aw, sa);
-    const __m256i p32 = _mm256_madd_epi16(p16, _mm256_set1_epi16(1));
-    __m128i s = _mm_add_epi32(_mm256_castsi256_si128(p32), _mm256_extracti128_si256(p32, 1));
-    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0x4E));
-    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0xB1));
-    return _mm_cvtsi128_si32(s);
+    const __m256i p16 = _mm256_maddubs_epi16(_mm256_sign_epi8(w, w), _mm256_sign_epi8(a, w));   /* |w| * (a*sign w) */
+    return _mm256_madd_epi16(p16, _mm256_set1_epi16(1));
 }
-static int have_avx2(void) {
-    static int v = -1;
-    if (v < 0) v = __builtin_cpu_supports("avx2") ? 1 : 0;
-    return v;
-}
+#define REF_HAVE_SIMD 1
 #else
-static int have_avx2(void) { return 0; }
+#define REF_HAVE_SIMD 0
 #endif
 
-/* ggml_vec_dot_q4_0_q8_0, generic path [upstream] */
+/* ggml_vec_dot_q4_0_q8_0, generic path [upstream]: sumf += sumi * d_w * d_a, block by block */
 float ref_vec_dot_q4_0_q8_0(int64_t n, const void *vx, const void *vy) {
     const blk_q4_0 *x = (const blk_q4_0 *)vx;
     const blk_q8_0 *y = (const blk_q8_0 *)vy;
     float sumf = 0;
     const int64_t nb = n / 32;
-#if defined(__x86_64__)
-    if (have_avx2()) {
-        for (int64_t i = 0; i < nb; i++) {
-            const int sumi = q4_0_q8_0_sumi_avx2(&x[i], &y[i]);
-            sumf += sumi * h2f(x[i].d) * h2f(y[i].d);
-        }
-        return sumf;
+    int64_t i = 0;
+#if REF_HAVE_SIMD
+    /* eight blocks at a time: the integer sums are reduced with a hadd tree (exact), the
+     * per-block float terms are formed with the same two roundings as the scalar code and
+     * then added to sumf one after the other, in block order. */
+    for (; i + 8 <= nb; i += 8) {
+        __m256i p[8];
+        for (int j = 0; j < 8; j++) p[j] = q4_0_q8_0_p32(&x[i + j], &y[i + j]);
+        const __m256i h01 = _mm256_hadd_epi32(p[0], p[1]), h23 = _mm256_hadd_epi32(p[2], p[3]);
+        const __m256i h45 = _mm256_hadd_epi32(p[4], p[5]), h67 = _mm256_hadd_epi32(p[6], p[7]);
+        const __m256i h0123 = _mm256_hadd_epi32(h01, h23), h4567 = _mm256_hadd_epi32(h45, h67);
+        /* lanes: lo128 = partial(0..3 | 4..7 of low halves), hi128 = same of high halves */
+        const __m128i s0123 = _mm_add_epi32(_mm256_castsi256_si128(h0123), _mm256_extracti128_si256(h0123, 1));
+        const __m128i s4567 = _mm_add_epi32(_mm256_castsi256_si128(h4567), _mm256_extracti128_si256(h4567, 1));
+        float si[8], dx[8], dy[8];
+        _mm_storeu_ps(si, _mm_cvtepi32_ps(s0123));
+        _mm_storeu_ps(si + 4, _mm_cvtepi32_ps(s4567));
+        for (int j = 0; j < 8; j++) { dx[j] = h2f(x[i + j].d); dy[j] = h2f(y[i + j].d); }
+        for (int j = 0; j < 8; j++) sumf += si[j] * dx[j] * dy[j];
     }
 #endif
-    for (int64_t i = 0; i < nb; i++) {
+    for (; i < nb; i++) {
         int sumi = 0;
         for (int j = 0; j < 16; j++) {
             const int v0 = (x[i].qs[j] & 0x0F) - 8, v1 = (x[i].qs[j] >> 4) - 8;

@@ -1,0 +1,128 @@
+"""Parity of the individual CUDA kernels with the CPU oracle, called through the C ABI.
+Bit-exact for dequantisation (integer/byte work); for the W4A8 GEMV the integer block dots
+are exact and only the f32 accumulation order differs, so the tolerance is a few ulps of the
+row's magnitude."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TYPES = {"Q4_0": (2, 32, 18), "Q8_0": (8, 32, 34), "Q4_K": (12, 256, 144), "Q6_K": (14, 256, 210)}
+
+
+@pytest.mark.parametrize("name", list(TYPES))
+def test_dequant_bit_exact_vs_golden(pkg, golden, name):
+    t, bs, _ = TYPES[name]
+    blocks, want = golden[f"{name}_blocks"], golden[f"{name}_deq"]
+    got = pkg.engine.dequantize(t, blocks, want.size).reshape(want.shape)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("name", list(TYPES))
+def test_dequant_bit_exact_vs_oracle_random(pkg, oracle, name):
+    from gguf import GGMLQuantizationType as T
+    t, bs, ts = TYPES[name]
+    rng = np.random.default_rng(7)
+    blocks = pkg.synth.random_blocks(T(t), 33, 4 * 256, 0.05, rng)
+    want = oracle.dequantize(t, blocks, 1024)
+    got = pkg.engine.dequantize(t, blocks, want.size).reshape(want.shape)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_dequant_empty_input_is_a_no_op(pkg):
+    assert pkg.engine.dequantize(2, np.zeros(0, np.uint8), 0).size == 0
+
+
+@pytest.mark.parametrize("name", list(TYPES))
+@pytest.mark.parametrize("rows,k", [(2, 256), (6, 1024), (10, 2560 if True else 0), (4, 11008 // 256 * 256)])
+def test_repack_then_dequant_equals_dequant(pkg, oracle, name, rows, k):
+    """The load-time split-plane layout must decode to exactly what the file blocks decode to."""
+    from gguf import GGMLQuantizationType as T
+    t, bs, ts = TYPES[name]
+    if k % bs:
+        pytest.skip("k not a multiple of the block size")
+    rng = np.random.default_rng(rows * 1000 + k)
+    blocks = pkg.synth.random_blocks(T(t), rows, k, 0.05, rng)
+    want = oracle.dequantize(t, blocks, k)
+    got = pkg.engine.dequantize_repacked(t, blocks, rows, k)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+GEMV_SHAPES = [(2, 256), (64, 4096), (130, 1024), (32, 11008), (48, 2560), (20, 5120), (16, 8192), (8, 14336), (8, 28672)]
+
+
+@pytest.mark.parametrize("name", list(TYPES))
+@pytest.mark.parametrize("rows,k", GEMV_SHAPES)
+def test_gemv_matches_oracle(pkg, oracle, name, rows, k):
+    from gguf import GGMLQuantizationType as T
+    t, bs, ts = TYPES[name]
+    if k % bs:
+        pytest.skip("k not a multiple of the block size")
+    rng = np.random.default_rng(rows + k)
+    W = pkg.synth.random_blocks(T(t), rows, k, k ** -0.5, rng)
+    x = rng.standard_normal(k).astype(np.float32)
+    want = oracle.mul_mat_vec(t, W, rows, k, x, faithful=True)
+    got = pkg.engine.gemv(t, W, rows, k, x)
+    tol = 4e-6 * np.abs(want).max() + 1e-6
+    assert np.max(np.abs(got - want)) <= tol * 8, (np.max(np.abs(got - want)), tol)
+
+
+@pytest.mark.parametrize("name", ["Q4_0", "Q6_K"])
+def test_gemv_with_fused_rmsnorm_matches_oracle(pkg, oracle, name):
+    from gguf import GGMLQuantizationType as T
+    t, bs, ts = TYPES[name]
+    rows, k = 96, 4096
+    rng = np.random.default_rng(11)
+    W = pkg.synth.random_blocks(T(t), rows, k, k ** -0.5, rng)
+    x = (rng.standard_normal(k) * 3).astype(np.float32)
+    g = (1 + 0.02 * rng.standard_normal(k)).astype(np.float32)
+    xn = oracle.rms_norm(x, g, 1e-5)
+    want = oracle.mul_mat_vec(t, W, rows, k, xn, faithful=True)
+    got = pkg.engine.gemv(t, W, rows, k, x, gain=g, eps=1e-5)
+    assert np.max(np.abs(got - want)) <= 5e-5 * np.abs(want).max() + 1e-6
+
+
+def test_gemv_edge_inputs(pkg, oracle):
+    """All-zero activations (d == 0 branch of the quantiser), a single spike, constant rows."""
+    from gguf import GGMLQuantizationType as T
+    rng = np.random.default_rng(5)
+    rows, k = 8, 512
+    for t in (2, 12, 14):
+        W = pkg.synth.random_blocks(T(t), rows, k, 0.05, rng)
+        for x in (np.zeros(k, np.float32), np.eye(1, k, 37, dtype=np.float32)[0] * 100, np.full(k, 0.25, np.float32)):
+            want = oracle.mul_mat_vec(t, W, rows, k, x, faithful=True)
+            got = pkg.engine.gemv(t, W, rows, k, x)
+            assert np.max(np.abs(got - want)) <= 1e-5 * max(1.0, np.abs(want).max()), (t, np.abs(got - want).max())
+
+
+def _attn_ref(q, k, v, n_head, n_head_kv, hd, scale):
+    """llama.cpp non-flash path in numpy (same steps as oracle/ggml_ref.c `attend`)."""
+    n = k.shape[0]
+    grp = n_head // n_head_kv
+    out = np.zeros(n_head * hd, np.float32)
+    q16 = q.astype(np.float16).astype(np.float64)
+    for h in range(n_head):
+        kh = k[:, (h // grp) * hd:(h // grp + 1) * hd].astype(np.float64)
+        vh = v[:, (h // grp) * hd:(h // grp + 1) * hd].astype(np.float64)
+        s = (kh @ q16[h * hd:(h + 1) * hd]).astype(np.float32) * np.float32(scale)
+        p = np.exp(s - s.max()).astype(np.float32)
+        p = (p / np.float32(p.astype(np.float64).sum())).astype(np.float16).astype(np.float64)
+        out[h * hd:(h + 1) * hd] = (p @ vh).astype(np.float32)
+    return out
+
+
+@pytest.mark.parametrize("n_ctx", [1, 2, 63, 64, 65, 300, 1024, 2500])
+@pytest.mark.parametrize("n_head,n_head_kv,hd", [(4, 4, 128), (8, 2, 64), (8, 1, 128), (4, 2, 80)])
+@pytest.mark.parametrize("cluster", [1, 4, 8])
+def test_attention_matches_reference(pkg, n_ctx, n_head, n_head_kv, hd, cluster):
+    if cluster == 8 and n_ctx not in (65, 2500):
+        pytest.skip("covered by the other cluster sizes")
+    rng = np.random.default_rng(n_ctx * 7 + n_head)
+    q = rng.standard_normal(n_head * hd).astype(np.float32)
+    k = rng.standard_normal((n_ctx, n_head_kv * hd)).astype(np.float16)
+    v = rng.standard_normal((n_ctx, n_head_kv * hd)).astype(np.float16)
+    scale = hd ** -0.5
+    want = _attn_ref(q, k, v, n_head, n_head_kv, hd, scale)
+    got = pkg.engine.attn_decode(q, k, v, n_head, n_head_kv, hd, scale, cluster)
+    # f16-rounded probabilities in the reference vs f32 here: <= 1e-3 relative (see attn.cu)
+    assert np.max(np.abs(got - want)) <= 1e-3 * max(1.0, np.abs(want).max()), np.max(np.abs(got - want))
