@@ -456,10 +456,11 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
     const int n_cons_warps = c.G * c.S, ntc = n_cons_warps * 32;
     constexpr int NP = TYPE == T_Q4_0 || TYPE == T_Q8_0 ? 2 : TYPE == T_Q4_K ? 3 : 4;
 
-    // tiles owned by this CTA
-    const int t0 = (int)((long long)blockIdx.x * c.n_tiles / gridDim.x);
-    const int t1 = (int)((long long)(blockIdx.x + 1) * c.n_tiles / gridDim.x);
-    const int my_tiles = t1 - t0;
+    // Rows owned by this CTA: an even split of the row PAIRS over the grid (pairs, because the
+    // RoPE / SiLU-gate epilogues consume two adjacent rows), walked in tiles of RT rows.
+    const int64_t pairs = a.W.rows >> 1;
+    const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
+    const int my_tiles = (int)((r_end - r_begin + c.RT - 1) / c.RT);
 
     if (tid == 0) {
         for (int s = 0; s < c.NS; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], n_cons_warps); }
@@ -475,8 +476,8 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
             for (int it = 0; it < my_tiles; it++) {
                 const int s = it % c.NS;
                 if (it >= c.NS) mbar_wait(&empty[s], ((it / c.NS) - 1) & 1);
-                const int64_t row0 = (int64_t)(t0 + it) * c.RT;
-                const int rows_here = (int)min((int64_t)c.RT, a.W.rows - row0);
+                const int64_t row0 = r_begin + (int64_t)it * c.RT;
+                const int rows_here = (int)min((int64_t)c.RT, r_end - row0);
                 uint32_t total = 0;
 #pragma unroll
                 for (int p = 0; p < NP; p++) total += (uint32_t)rows_here * a.W.stride[p];
@@ -516,8 +517,8 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
     for (int it = 0; it < my_tiles; it++) {
         const int s = it % c.NS;
         mbar_wait(&full[s], (it / c.NS) & 1);
-        const int64_t row0 = (int64_t)(t0 + it) * c.RT;
-        const int rows_here = (int)min((int64_t)c.RT, a.W.rows - row0);
+        const int64_t row0 = r_begin + (int64_t)it * c.RT;
+        const int rows_here = (int)min((int64_t)c.RT, r_end - row0);
         const uint8_t* sp = stages + (size_t)s * c.stage_bytes;
         float* redt = red + (size_t)(it & 1) * c.RT * c.S;
         for (int rr = 0; rr < c.RPG; rr++) {
@@ -637,7 +638,7 @@ int gemv_launch(const GemvArgs& a, cudaStream_t st, bool pdl, const GemvTune* tu
     c.NS = ns;
     const size_t smem = off + (size_t)ns * c.stage_bytes;
     c.n_tiles = (int)((W.rows + c.RT - 1) / c.RT);
-    const int grid = min(c.n_tiles, sm_count() * ctas_per_sm);
+    const int grid = (int)min((int64_t)(W.rows / 2), (int64_t)sm_count() * ctas_per_sm);
     const int threads = (c.G * c.S + 1) * 32;
 
 #define B2_GEMV_CASE(T, N) if (W.type == T && nb == N) return launch_t<T, N>(a, c, grid, threads, smem, st, pdl)
