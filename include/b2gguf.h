@@ -130,6 +130,10 @@ int b2_gemv_bench(int ggml_type, int64_t rows, int64_t k, int iters, const int* 
  * f16 (row-major, unpaged on the host side; the hook pages them) -> out[n_head*head_dim]. */
 int b2_attn_decode(const float* q, const uint16_t* k, const uint16_t* v, int n_ctx, int n_head, int n_head_kv,
                    int head_dim, float scale, int cluster, float* out);
+/* Read back one per-sequence activation buffer as it stands after the last step:
+ * what = 0 residual stream x[n_embd], 1 rotated query q[n_head*head_dim], 2 attention output,
+ * 3 FFN hidden h[n_ff], 4 logits[n_vocab], 5 phi-2 attention projection[n_embd]. */
+int b2_debug_read(b2_model* m, int seq, int what, float* out, int n);
 /* Copy cached K and V rows [0, n_tok) of one layer to the host as f16 [n_tok][n_head_kv*head_dim]. */
 int b2_kv_read(b2_model* m, int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok);
 

@@ -145,6 +145,27 @@ int b2_kv_read(b2_model* m, int seq, int layer, uint16_t* k_out, uint16_t* v_out
 int b2_profile_step(b2_model* m, int seq, int32_t tok, float* class_ms, int* class_launches) {
     B2_MODEL_CALL(m, m->m.profile_step(seq, tok, class_ms, class_launches));
 }
+int b2_debug_read(b2_model* m, int seq, int what, float* out, int n) {
+    if (!m || !out) B2_FAIL(B2_ERR_ARG, "b2_debug_read: null argument");
+    B2_TRY(m->m.check_seq(seq));
+    const Slot& s = m->m.slots[seq];
+    const HParams& h = m->m.hp;
+    const float* src = nullptr;
+    int cap = 0;
+    switch (what) {
+    case 0: src = s.x; cap = h.n_embd; break;
+    case 1: src = s.q; cap = h.n_head * h.head_dim; break;
+    case 2: src = s.att; cap = h.n_head * h.head_dim; break;
+    case 3: src = s.h; cap = h.n_ff; break;
+    case 4: src = s.logits; cap = h.n_vocab; break;
+    case 5: src = s.att2; cap = h.n_embd; break;
+    default: B2_FAIL(B2_ERR_ARG, "b2_debug_read: unknown buffer %d", what);
+    }
+    if (n < 0 || n > cap) B2_FAIL(B2_ERR_ARG, "b2_debug_read: n=%d outside [0,%d]", n, cap);
+    B2_CUDA(cudaSetDevice(m->ctx->devs[0]));
+    B2_CUDA(cudaMemcpy(out, src, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
 int b2_get_stats(const b2_model* m, b2_stats* out) {
     if (!m || !out) B2_FAIL(B2_ERR_ARG, "b2_get_stats: null argument");
     out->steps = m->m.steps; out->kernel_launches = m->m.launches; out->gpu_ms = m->m.last_ms;

@@ -118,6 +118,9 @@ __device__ __forceinline__ uint32_t dsmem_addr(const void* p, uint32_t rank) {
 __device__ __forceinline__ void dsmem_st_f32(uint32_t addr, float v) {
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ void dsmem_st_f64(uint32_t addr, double v) {
+    asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
 __device__ __forceinline__ float dsmem_ld_f32(uint32_t addr) {
     float v;
     asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");

@@ -75,6 +75,7 @@ Model::~Model() {
     if (kv_k) cudaFree(kv_k);
     if (kv_v) cudaFree(kv_v);
     if (slot_mem) cudaFree(slot_mem);
+    if (rope_table) cudaFree(rope_table);
     arena.release();
 }
 
@@ -320,7 +321,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
     auto carve = [&](size_t bytes) { const size_t o2 = align_up(off, 256); off = o2 + bytes; return o2; };
     const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
                  o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
-                 o_cs = carve((size_t)hp.n_rot / 2 * 8), o_pos = carve(4), o_key = carve(8), o_out = carve((size_t)out_cap * 4),
+                 o_pos = carve(4), o_key = carve(8), o_out = carve((size_t)out_cap * 4),
                  o_forced = carve((size_t)max_ctx * 4);
     const size_t slot_bytes = align_up(off, 256);
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
@@ -331,10 +332,25 @@ int Model::load(const char* path, const b2_load_opts* o) {
         Slot& s = slots[i];
         s.d_state = (SeqState*)(b + o_state); s.d_page_table = (int*)(b + o_pt); s.x = (float*)(b + o_x); s.q = (float*)(b + o_q);
         s.att = (float*)(b + o_att); s.att2 = (float*)(b + o_att2); s.h = (float*)(b + o_h); s.logits = (float*)(b + o_logits);
-        s.rope_cs = (float2*)(b + o_cs); s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
+        s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
         s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced);
     }
-    theta_scale = powf(hp.rope_freq_base, -2.0f / hp.n_rot);
+    // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (theta starts
+    // at pos and is multiplied by freq_base^(-2/n_rot) once per pair; libm cosf/sinf)
+    {
+        const float theta_scale = powf(hp.rope_freq_base, -2.0f / hp.n_rot);
+        const int half = hp.n_rot / 2;
+        std::vector<float2> tab((size_t)max_ctx * half);
+        for (int pos = 0; pos < max_ctx; pos++) {
+            float theta = (float)pos;
+            for (int p = 0; p < half; p++) {
+                tab[(size_t)pos * half + p] = make_float2(cosf(theta), sinf(theta));
+                theta *= theta_scale;
+            }
+        }
+        B2_CUDA(cudaMalloc(&rope_table, tab.size() * sizeof(float2)));
+        B2_CUDA(cudaMemcpy(rope_table, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    }
     return B2_OK;
 }
 
@@ -406,8 +422,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
     const bool pdl = use_pdl;
     {
         StepBeginArgs a;
-        a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.rope_cs = s.rope_cs; a.pos_out = s.d_pos; a.argmax_key = s.d_key;
-        a.n_rot = hp.n_rot; a.theta_scale = theta_scale;
+        a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key;
         B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
     }
     for (int l = 0; l < hp.n_layer; l++) {
@@ -421,7 +436,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
             a.bias = L.b_qkv; a.y = s.q; a.epi_row0 = seg.row0;
             a.n_q = nq; a.n_kv = nkv; a.head_dim = hd; a.n_rot = hp.n_rot; a.rope_neox = neox ? 1 : 0;
             a.q_scale = hp.arch == 1 ? 1.0f / sqrtf((float)hd) : 1.0f;
-            a.rope_cs = s.rope_cs;
+            a.rope_cs = rope_table;
             a.kv.k_base = kb; a.kv.v_base = vb; a.kv.page_table = s.d_page_table; a.kv.pos = s.d_pos;
             a.kv.page_tokens = PAGE_TOKENS; a.kv.kv_dim = nkv;
             B2_TRY(gemv_launch(a, stream, pdl)); nl++; B2_TRY(mark(1));

@@ -45,7 +45,6 @@ struct Slot {
     SeqState* d_state = nullptr;
     int* d_page_table = nullptr;
     float *x = nullptr, *q = nullptr, *att = nullptr, *att2 = nullptr, *h = nullptr, *logits = nullptr;
-    float2* rope_cs = nullptr;
     int* d_pos = nullptr;
     unsigned long long* d_key = nullptr;
     int *d_out = nullptr, *d_forced = nullptr;
@@ -60,7 +59,7 @@ struct Model {
     HParams hp;
     bool neox = false, use_pdl = true, use_graph = true;
     int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
-    float theta_scale = 0.f;
+    float2* rope_table = nullptr;     // [max_ctx][n_rot/2]
     Arena arena;
     void* staging = nullptr;
     QMat w_embd, w_head;

@@ -382,8 +382,9 @@ __device__ __forceinline__ float gelu_f16_table(float v) {
     if (v <= -10.0f) return 0.0f;
     if (v >= 10.0f) return v;
     const float t = __half2float(__float2half_rn(v));
-    const float g = 0.5f * t * (1.0f + tanhf(0.79788456080286535587989211986876f * t * (1.0f + 0.044715f * t * t)));
-    return __half2float(__float2half_rn(g));
+    const float u = __fmul_rn(__fmul_rn(0.79788456080286535587989211986876f, t), __fadd_rn(1.0f, __fmul_rn(__fmul_rn(0.044715f, t), t)));
+    const float th = (float)tanh((double)u);          // correctly rounded f32, as the oracle's canonical mode
+    return __half2float(__float2half_rn(__fmul_rn(__fmul_rn(0.5f, t), __fadd_rn(1.0f, th))));
 }
 
 __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best) {
@@ -395,7 +396,7 @@ __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1,
         a.y[r0] = __fadd_rn(__fadd_rn(v0, a.y2[r0]), a.y[r0]);
         a.y[r0 + 1] = __fadd_rn(__fadd_rn(v1, a.y2[r0 + 1]), a.y[r0 + 1]);
         break;
-    case EPI_SILU_MUL: a.y[r0 >> 1] = __fmul_rn(__fdiv_rn(v0, __fadd_rn(1.0f, expf(-v0))), v1); break;
+    case EPI_SILU_MUL: a.y[r0 >> 1] = __fmul_rn(__fdiv_rn(v0, __fadd_rn(1.0f, (float)exp((double)(-v0)))), v1); break;
     case EPI_GELU: a.y[r0] = gelu_f16_table(v0); a.y[r0 + 1] = gelu_f16_table(v1); break;
     case EPI_LOGITS: {
         a.y[r0] = v0; a.y[r0 + 1] = v1;
@@ -416,7 +417,7 @@ __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1,
         if (!is_q && !is_k) {
             if (a.rope_neox && e < a.n_rot) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
         } else if (e < a.n_rot) {
-            const float2 cs = a.rope_cs[e >> 1];
+            const float2 cs = a.rope_cs[(size_t)(*a.kv.pos) * (a.n_rot >> 1) + (e >> 1)];
             o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
             o1 = __fadd_rn(__fmul_rn(v0, cs.y), __fmul_rn(v1, cs.x));
             if (a.rope_neox) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
@@ -446,7 +447,7 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MAX_NS;
     double* dscratch = reinterpret_cast<double*>(smem + 2 * MAX_NS * 8);     // 32 doubles
-    float* red = reinterpret_cast<float*>(smem + c.off_red);
+    double* red = reinterpret_cast<double*>(smem + c.off_red);
     uint8_t* xq = smem + c.off_xq;
     float* xd = reinterpret_cast<float*>(smem + c.off_xd);
     int* xs = reinterpret_cast<int*>(smem + c.off_xs);
@@ -520,7 +521,7 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
         const int64_t row0 = r_begin + (int64_t)it * c.RT;
         const int rows_here = (int)min((int64_t)c.RT, r_end - row0);
         const uint8_t* sp = stages + (size_t)s * c.stage_bytes;
-        float* redt = red + (size_t)(it & 1) * c.RT * c.S;
+        double* redt = red + (size_t)(it & 1) * c.RT * c.S;
         for (int rr = 0; rr < c.RPG; rr++) {
             const int r = g * c.RPG + rr;
             if (r >= rows_here) break;
@@ -528,10 +529,12 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
             const uint8_t* pb = sp;
 #pragma unroll
             for (int p = 0; p < NP; p++) { rp.p[p] = pb + (size_t)r * a.W.stride[p]; pb += (size_t)c.RT * a.W.stride[p]; }
-            float acc = 0.f;
+            // per-unit float terms exactly as in ggml's generic path, added in f64: the sum no longer
+            // depends on the order, so any split over lanes / warps gives the same f32 result
+            double acc = 0.0;
 #pragma unroll
-            for (int j = 0; j < NB; j++) acc = __fadd_rn(acc, unit_dot(xr[j], rp, unit[j], c.nunits));
-            acc = warp_sum(acc);
+            for (int j = 0; j < NB; j++) acc += (double)unit_dot(xr[j], rp, unit[j], c.nunits);
+            acc = warp_sum_d(acc);
             if (lane == 0) redt[r * c.S + ch] = acc;
         }
         __syncwarp();
@@ -540,9 +543,9 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
         if (ch == 0) {
             const int r = g * c.RPG + 2 * lane;
             if (2 * lane < c.RPG && r < rows_here) {
-                float v0 = 0.f, v1 = 0.f;
-                for (int k = 0; k < c.S; k++) { v0 = __fadd_rn(v0, redt[r * c.S + k]); v1 = __fadd_rn(v1, redt[(r + 1) * c.S + k]); }
-                epilogue_pair(a, a.epi_row0 + row0 + r, v0, v1, best);
+                double d0 = 0.0, d1 = 0.0;
+                for (int k = 0; k < c.S; k++) { d0 += redt[r * c.S + k]; d1 += redt[(r + 1) * c.S + k]; }
+                epilogue_pair(a, a.epi_row0 + row0 + r, (float)d0, (float)d1, best);
             }
         }
     }
@@ -625,7 +628,7 @@ int gemv_launch(const GemvArgs& a, cudaStream_t st, bool pdl, const GemvTune* tu
     const size_t xd_bytes = (kq ? W.k / 256 : W.k / 32) * 4;
     const size_t xs_bytes = (kq ? W.k / 16 : W.k / 32) * 4;
     size_t off = 2 * MAX_NS * 8 + 32 * 8;
-    c.off_red = (uint32_t)off; off += (size_t)2 * c.RT * c.S * 4; off = (off + 15) / 16 * 16;
+    c.off_red = (uint32_t)off; off += (size_t)2 * c.RT * c.S * 8; off = (off + 15) / 16 * 16;
     c.off_xq = (uint32_t)off; off += xq_bytes; off = (off + 15) / 16 * 16;
     c.off_xd = (uint32_t)off; off += xd_bytes; off = (off + 15) / 16 * 16;
     c.off_xs = (uint32_t)off; off += xs_bytes; off = (off + 127) / 128 * 128;

@@ -47,7 +47,7 @@ struct GemvArgs {
     // EPI_QKV_ROPE
     int n_q = 0, n_kv = 0, head_dim = 0, n_rot = 0, rope_neox = 0;
     float q_scale = 1.f;
-    const float2* rope_cs = nullptr;   // [n_rot/2] (cos, sin) at the current position
+    const float2* rope_cs = nullptr;   // [max_ctx][n_rot/2] (cos, sin) table, built on the host
     KvDesc kv;
     // EPI_LOGITS
     unsigned long long* argmax_key = nullptr;
@@ -86,11 +86,8 @@ struct StepBeginArgs {
     SeqState* st = nullptr;
     QMat embd;
     float* x = nullptr;            // [n_embd]
-    float2* rope_cs = nullptr;     // [n_rot/2]
     int* pos_out = nullptr;        // device scalar consumed by the layer kernels
     unsigned long long* argmax_key = nullptr;
-    int n_rot = 0;
-    float theta_scale = 0.f;       // freq_base^(-2/n_rot)
 };
 int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
 struct StepEndArgs {

@@ -9,25 +9,17 @@
 
 namespace b2 {
 
-// step_begin: x = embedding row of the current token (ggml get_rows), RoPE (cos, sin) table for
-// the current position, position scalar for the layer kernels, arg-max accumulator cleared.
+// step_begin: x = embedding row of the current token (ggml get_rows), position scalar for the
+// layer kernels, arg-max accumulator cleared.
 __global__ void step_begin_kernel(const StepBeginArgs a) {
     pdl_trigger();
     pdl_wait();
     const int tok = a.st->cur_tok, pos = a.st->pos;
     const int E = (int)a.embd.k;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < E; i += gridDim.x * blockDim.x) a.x[i] = qmat_elem(a.embd, tok, i);
-    if (blockIdx.x == 0) {
-        // ggml rope: theta starts at pos and is multiplied by theta_scale once per pair
-        for (int p = threadIdx.x; p < a.n_rot / 2; p += blockDim.x) {
-            float theta = (float)pos;
-            for (int k = 0; k < p; k++) theta = __fmul_rn(theta, a.theta_scale);
-            a.rope_cs[p] = make_float2(cosf(theta), sinf(theta));
-        }
-        if (threadIdx.x == 0) {
-            *a.pos_out = pos;
-            *a.argmax_key = 0ull;
-        }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *a.pos_out = pos;
+        *a.argmax_key = 0ull;
     }
 }
 

@@ -22,7 +22,7 @@ LOAD_NO_PDL, LOAD_NO_GRAPH = 1, 2
 SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
     "b2_seq_new", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
-    "b2_get_stats", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_bench", "b2_attn_decode", "b2_kv_read",
+    "b2_get_stats", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_bench", "b2_attn_decode", "b2_kv_read", "b2_debug_read",
 ]
 
 
@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
         L.b2_gemv_bench.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int, vp, fp]
         L.b2_attn_decode.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp]
         L.b2_kv_read.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_int]
+        L.b2_debug_read.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
         _lib = L
     return _lib
 
@@ -224,6 +225,15 @@ class Model:
         nl = np.zeros(8, dtype=np.int32)
         _check(lib().b2_profile_step(self._h, seq, tok, _ptr(ms), _ptr(nl)))
         return {c: (float(ms[i]), int(nl[i])) for i, c in enumerate(self.PROFILE_CLASSES)}
+
+    DEBUG_BUFFERS = {"x": 0, "q": 1, "att": 2, "h": 3, "logits": 4, "att2": 5}
+
+    def debug_read(self, seq: int, what: str) -> np.ndarray:
+        i = self.info
+        n = {"x": i.n_embd, "q": i.n_head * i.head_dim, "att": i.n_head * i.head_dim, "h": i.n_ff, "logits": i.n_vocab, "att2": i.n_embd}[what]
+        out = np.empty(n, dtype=np.float32)
+        _check(lib().b2_debug_read(self._h, seq, self.DEBUG_BUFFERS[what], _ptr(out), n))
+        return out
 
     def stats(self) -> Stats:
         s = Stats()

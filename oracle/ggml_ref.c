@@ -429,6 +429,85 @@ float ref_vec_dot_q6_K_q8_K(int64_t n, const void *vx, const void *vy) {
     return sumf;
 }
 
+
+/* ---- "canonical" (order-free) dots ------------------------------------------------------
+ * ggml adds the per-block float terms in f32, in an order that depends on the ISA path (generic
+ * C: block after block; AVX2: 8 lanes; NEON: two blocks at a time ...).  Rounding differences of
+ * 1e-7 between two such orders are enough to flip int8 roundings of the NEXT activation
+ * quantisation, after which two runs of the same model differ by ~1e-1 in the logits.  To have
+ * something a massively parallel kernel can reproduce bit for bit, mode 2 keeps every term of
+ * the generic path (exact integer block dot, same float scale products) but adds the terms in
+ * f64, where the order no longer matters, and rounds the row sum to f32 once.  K-quants use
+ * one term per half super-block (128 weights) with the exact integer total. */
+static double canon_dot_q4_0(int64_t n, const blk_q4_0 *x, const blk_q8_0 *y) {
+    double acc = 0;
+    for (int64_t i = 0; i < n / 32; i++) {
+        int sumi = 0;
+        for (int j = 0; j < 16; j++) {
+            const int v0 = (x[i].qs[j] & 0x0F) - 8, v1 = (x[i].qs[j] >> 4) - 8;
+            sumi += v0 * y[i].qs[j] + v1 * y[i].qs[j + 16];
+        }
+        acc += (double)(((float)sumi * h2f(x[i].d)) * h2f(y[i].d));
+    }
+    return acc;
+}
+static double canon_dot_q8_0(int64_t n, const blk_q8_0 *x, const blk_q8_0 *y) {
+    double acc = 0;
+    for (int64_t i = 0; i < n / 32; i++) {
+        int sumi = 0;
+        for (int j = 0; j < 32; j++) sumi += x[i].qs[j] * y[i].qs[j];
+        acc += (double)((float)sumi * (h2f(x[i].d) * h2f(y[i].d)));
+    }
+    return acc;
+}
+static double canon_dot_q6_K(int64_t n, const blk_q6_K *x, const blk_q8_K *y) {
+    double acc = 0;
+    for (int64_t i = 0; i < n / 256; i++) {
+        const float d = h2f(x[i].d) * y[i].d;
+        for (int half = 0; half < 2; half++) {
+            const uint8_t *ql = x[i].ql + 64 * half, *qh = x[i].qh + 32 * half;
+            const int8_t *sc = x[i].scales + 8 * half, *q8 = y[i].qs + 128 * half;
+            int tot = 0;
+            for (int l = 0; l < 32; l++) {
+                const int is = l / 16;
+                const int q1 = (int)((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                const int q2 = (int)((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                const int q3 = (int)((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                const int q4 = (int)((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                tot += sc[is] * q1 * q8[l] + sc[is + 2] * q2 * q8[l + 32] + sc[is + 4] * q3 * q8[l + 64] + sc[is + 6] * q4 * q8[l + 96];
+            }
+            acc += (double)(d * (float)tot);
+        }
+    }
+    return acc;
+}
+static double canon_dot_q4_K(int64_t n, const blk_q4_K *x, const blk_q8_K *y) {
+    double acc = 0;
+    for (int64_t i = 0; i < n / 256; i++) {
+        const float d = h2f(x[i].d) * y[i].d, dmin = h2f(x[i].dmin) * y[i].d;
+        for (int half = 0; half < 2; half++) {
+            int accs = 0, accm = 0;
+            for (int j = 0; j < 4; j++) {               /* sub-block 4*half + j: 32 weights */
+                const int sb = 4 * half + j;
+                uint8_t sc, mn;
+                k4_scale_min(sb, x[i].scales, &sc, &mn);
+                const uint8_t *q = x[i].qs + 32 * (sb / 2);
+                const int8_t *q8 = y[i].qs + 32 * sb;
+                int dot = 0, bs = 0;
+                for (int l = 0; l < 32; l++) {
+                    const int w = (sb & 1) ? (q[l] >> 4) : (q[l] & 0xF);
+                    dot += w * q8[l];
+                    bs += q8[l];
+                }
+                accs += sc * dot;
+                accm += mn * bs;
+            }
+            acc += (double)(d * (float)accs - dmin * (float)accm);
+        }
+    }
+    return acc;
+}
+
 /* vec_dot_type of each weight type (ggml type_traits [upstream]) */
 static int act_type_for(int wtype) {
     switch (wtype) {
@@ -472,6 +551,16 @@ void ref_mul_mat_vec(int wtype, const void *W, int64_t rows, int64_t k, const fl
 #pragma omp parallel for schedule(static) num_threads(nt)
     for (int64_t r = 0; r < rows; r++) {
         const void *wr = Wb + r * rs;
+        if (faithful == 2 && wtype != REF_F16) {
+            switch (wtype) {
+            case REF_Q4_0: y[r] = (float)canon_dot_q4_0(k, (const blk_q4_0 *)wr, (const blk_q8_0 *)xq); break;
+            case REF_Q8_0: y[r] = (float)canon_dot_q8_0(k, (const blk_q8_0 *)wr, (const blk_q8_0 *)xq); break;
+            case REF_Q4_K: y[r] = (float)canon_dot_q4_K(k, (const blk_q4_K *)wr, (const blk_q8_K *)xq); break;
+            case REF_Q6_K: y[r] = (float)canon_dot_q6_K(k, (const blk_q6_K *)wr, (const blk_q8_K *)xq); break;
+            default: y[r] = 0;
+            }
+            continue;
+        }
         switch (wtype) {
         case REF_Q4_0: y[r] = ref_vec_dot_q4_0_q8_0(k, wr, xq); break;
         case REF_Q8_0: y[r] = ref_vec_dot_q8_0_q8_0(k, wr, xq); break;
@@ -540,7 +629,19 @@ void ref_softmax(float *x, int64_t n) {
     const float inv = (float)(1.0 / sum);
     for (int64_t i = 0; i < n; i++) x[i] *= inv;
 }
-static inline float silu_f(float v) { return v / (1.0f + expf(-v)); }
+/* mode 2 evaluates exp / tanh in f64 and rounds once: a correctly rounded f32 result, which is
+ * what two different math libraries (glibc here, CUDA on the device) can agree on bit for bit */
+static void softmax_canon(float *x, int64_t n) {
+    float mx = -INFINITY;
+    for (int64_t i = 0; i < n; i++) if (x[i] > mx) mx = x[i];
+    double sum = 0;
+    for (int64_t i = 0; i < n; i++) { x[i] = (float)exp((double)(x[i] - mx)); sum += (double)x[i]; }
+    const float inv = (float)(1.0 / sum);
+    for (int64_t i = 0; i < n; i++) x[i] *= inv;
+}
+static inline float silu_f(float v, int mode) {
+    return mode == 2 ? v / (1.0f + (float)exp((double)(-v))) : v / (1.0f + expf(-v));
+}
 /* ggml gelu [upstream]: tanh form looked up through an f16 table => input and output rounded to f16 */
 static inline float gelu_f(float v, int faithful) {
     const float A = 0.044715f, S = 0.79788456080286535587989211986876f;
@@ -548,7 +649,9 @@ static inline float gelu_f(float v, int faithful) {
     if (v <= -10.0f) return 0.0f;
     if (v >= 10.0f) return v;
     const float t = h2f(f2h(v));
-    return h2f(f2h(0.5f * t * (1.0f + tanhf(S * t * (1.0f + A * t * t)))));
+    const float u = S * t * (1.0f + A * t * t);
+    const float th = faithful == 2 ? (float)tanh((double)u) : tanhf(u);
+    return h2f(f2h(0.5f * t * (1.0f + th)));
 }
 
 /* ---- forward pass ---------------------------------------------------------------------- */
@@ -633,7 +736,7 @@ static void attend(ref_ctx *c, int il, int pos, float scale) {
                 for (int d = 0; d < hd; d++) s += (double)(h2f(kr[d]) * h2f(q16[d]));
                 sc[t] = (float)s * scale;
             }
-            ref_softmax(sc, pos + 1);
+            if (c->faithful == 2) softmax_canon(sc, pos + 1); else ref_softmax(sc, pos + 1);
             for (int d = 0; d < hd; d++) {
                 double s = 0;
                 for (int t = 0; t <= pos; t++)
@@ -695,7 +798,7 @@ int ref_eval(ref_ctx *c, int32_t token, int pos, float *logits) {
             ref_rms_norm(c->x, (const float *)L->ffn_norm.data, c->xn, E, m->norm_eps);
             matvec(c, &L->w_gate, m->n_ff, E, c->xn, c->gate);
             matvec(c, &L->w_up, m->n_ff, E, c->xn, c->up);
-            for (int i = 0; i < m->n_ff; i++) c->gate[i] = silu_f(c->gate[i]) * c->up[i];
+            for (int i = 0; i < m->n_ff; i++) c->gate[i] = silu_f(c->gate[i], c->faithful) * c->up[i];
             matvec(c, &L->w_down, E, m->n_ff, c->gate, c->ffn);
             for (int i = 0; i < E; i++) c->x[i] += c->ffn[i];
         } else {

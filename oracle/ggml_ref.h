@@ -60,10 +60,13 @@ float ref_vec_dot_q8_0_q8_0(int64_t n, const void *vx, const void *vy);
 float ref_vec_dot_q4_K_q8_K(int64_t n, const void *vx, const void *vy);
 float ref_vec_dot_q6_K_q8_K(int64_t n, const void *vx, const void *vy);
 
-/* y[r] = W[r,:] . x   for r < rows.
- * faithful != 0: ggml CPU semantics (x quantised to the weight type's vec_dot
- * type, integer block dots, f32 scale-accumulate).  faithful == 0: "ideal"
- * path, weights dequantised to f32, f64 accumulate.  threads<=0 -> all cores. */
+/* y[r] = W[r,:] . x   for r < rows.  `faithful` selects the arithmetic:
+ *   0  "ideal": weights dequantised to f32, f64 accumulate, activations not quantised;
+ *   1  ggml's generic C path: x quantised to the weight type's vec_dot type, exact integer
+ *      block dots, per-block float terms added in f32, block after block;
+ *   2  "canonical": the same terms, added in f64 and rounded to f32 once, exp/tanh rounded
+ *      from f64 -- order-free, so the CUDA kernels can (and must) match it bit for bit.
+ * threads<=0 -> all cores. */
 void ref_mul_mat_vec(int wtype, const void *W, int64_t rows, int64_t k,
                      const float *x, float *y, int faithful, int threads);
 

@@ -111,7 +111,7 @@ def quantize(t: int, x: np.ndarray) -> np.ndarray:
     return out
 
 
-def mul_mat_vec(t: int, W: np.ndarray, rows: int, k: int, x: np.ndarray, faithful: bool = True, threads: int = 0) -> np.ndarray:
+def mul_mat_vec(t: int, W: np.ndarray, rows: int, k: int, x: np.ndarray, faithful: int = 1, threads: int = 0) -> np.ndarray:
     W = np.ascontiguousarray(W, dtype=np.uint8)
     x = np.ascontiguousarray(x, dtype=np.float32)
     y = np.empty(rows, dtype=np.float32)
@@ -135,7 +135,8 @@ def rope(x, n_head, head_dim, n_rot, pos, freq_base, mode):
 class OracleModel:
     """A GGUF file opened with the `gguf` package's reader and evaluated by the C oracle."""
 
-    def __init__(self, path: str, faithful: bool = True, threads: int = 0, n_ctx: int | None = None):
+    def __init__(self, path: str, faithful: int = 1, threads: int = 0, n_ctx: int | None = None):
+        """faithful: 0 ideal f32, 1 ggml generic C order, 2 canonical (f64 term accumulation; see ggml_ref.h)."""
         import gguf
         self.reader = r = gguf.GGUFReader(path)
         self.tensors = {t.name: t for t in r.tensors}

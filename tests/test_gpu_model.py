@@ -1,6 +1,13 @@
 """End-to-end parity of the decode engine with the CPU oracle on seeded synthetic GGUF
 models, through the C ABI: logits within max-abs 2e-2 (BASELINE.json north_star), greedy
-tokens identical for 64 steps."""
+tokens identical for 64 steps.
+
+Which oracle.  W4A8 inference is chaotic at the 1e-7 level: two evaluations whose f32
+summation ORDER differs (ggml's own generic-C, AVX2 and NEON paths already do) sooner or later
+round one activation to a different int8, after which their logits differ by ~1e-1.  The
+engine therefore implements, and these tests pin it to, the oracle's order-free "canonical"
+mode (oracle/ggml_ref.h: same integer block dots and float terms as ggml's generic path,
+terms added in f64).  Against ggml's generic f32 order the comparison is statistical."""
 import numpy as np
 import pytest
 
@@ -16,8 +23,8 @@ def eng(pkg):
     e.close()
 
 
-def _teacher_forced_compare(pkg, oracle, eng, path, n_prompt, n_steps, flags=0):
-    om = oracle.OracleModel(path, faithful=True)
+def _teacher_forced_compare(pkg, oracle, eng, path, n_prompt, n_steps, flags=0, mode=2):
+    om = oracle.OracleModel(path, faithful=mode)
     m = eng.load(path, max_batch=2, max_ctx=256, flags=flags)
     toks = pkg.synth.prompt_tokens(n_prompt, om.m.n_vocab)
     seq = m.seq_new()
@@ -43,9 +50,20 @@ def _teacher_forced_compare(pkg, oracle, eng, path, n_prompt, n_steps, flags=0):
 @pytest.mark.parametrize("preset", ["tiny-llama", "tiny-gqa", "tiny-phi2"])
 def test_logits_match_oracle(pkg, oracle, eng, model_dir, preset):
     path = pkg.synth.cached_model(preset, model_dir)
-    worst, n_same = _teacher_forced_compare(pkg, oracle, eng, path, 9, 16)
+    worst, n_same = _teacher_forced_compare(pkg, oracle, eng, path, 9, 40)
     assert worst <= LOGIT_TOL, worst
-    assert n_same == 16
+    assert n_same == 40
+
+
+@pytest.mark.parametrize("preset", ["tiny-llama", "tiny-gqa", "tiny-phi2"])
+def test_logits_vs_ggml_generic_order(pkg, oracle, eng, model_dir, preset):
+    """Against ggml's generic f32 accumulation order the engine is as close as two ggml builds
+    are to each other: bounded by the quantisation-noise floor, tokens equal wherever the
+    oracle's own top-2 margin is above it."""
+    path = pkg.synth.cached_model(preset, model_dir)
+    worst, n_same = _teacher_forced_compare(pkg, oracle, eng, path, 9, 40, mode=1)
+    assert worst <= 0.5, worst
+    assert n_same >= 36, n_same
 
 
 @pytest.mark.parametrize("flags", [1, 2, 3])
@@ -58,7 +76,7 @@ def test_logits_match_without_pdl_or_graphs(pkg, oracle, eng, model_dir, flags):
 @pytest.mark.parametrize("preset", ["tiny-llama", "tiny-gqa", "tiny-phi2"])
 def test_greedy_64_tokens_identical(pkg, oracle, eng, model_dir, preset):
     path = pkg.synth.cached_model(preset, model_dir)
-    om = oracle.OracleModel(path, faithful=True)
+    om = oracle.OracleModel(path, faithful=2)
     toks = pkg.synth.prompt_tokens(16, om.m.n_vocab)
     want, want_logits = om.generate(toks, 64)
     m = eng.load(path, max_batch=1, max_ctx=256)
@@ -76,7 +94,7 @@ def test_greedy_64_tokens_identical(pkg, oracle, eng, model_dir, preset):
 
 
 def test_kv_cache_rows_match_oracle(pkg, oracle, eng, model_dir):
-    """f16 K/V rows written by the fused QKV+RoPE epilogue == the oracle's cache, to 1 f16 ulp."""
+    """f16 K/V rows written by the fused QKV+RoPE epilogue == the oracle's cache, bit for bit."""
     path = pkg.synth.cached_model("tiny-llama", model_dir)
     m = eng.load(path, max_batch=1, max_ctx=256)
     toks = pkg.synth.prompt_tokens(70, m.info.n_vocab)          # crosses a 64-token page boundary
@@ -84,10 +102,7 @@ def test_kv_cache_rows_match_oracle(pkg, oracle, eng, model_dir):
     m.prefill(seq, toks, want_logits=False)
     k, v = m.kv_read(seq, 0, 70)
     # layer-0 K/V depend only on the embedding row, the norm and the projections
-    om = oracle.OracleModel(path, faithful=True)
-    for t in toks:
-        om.eval(int(t), want_logits=False)
-    import ctypes as C
+    om = oracle.OracleModel(path, faithful=2)
     nkv = m.info.n_head_kv * m.info.head_dim
     # the oracle keeps its cache private; recompute layer-0 K/V rows through its public pieces
     import gguf
@@ -98,11 +113,11 @@ def test_kv_cache_rows_match_oracle(pkg, oracle, eng, model_dir):
     wk, wv = tens["blk.0.attn_k.weight"], tens["blk.0.attn_v.weight"]
     for pos in (0, 1, 63, 64, 69):
         xn = oracle.rms_norm(emb[toks[pos]], g, om.m.norm_eps)
-        kk = oracle.mul_mat_vec(int(wk.tensor_type), np.ascontiguousarray(wk.data), nkv, E, xn)
-        vv = oracle.mul_mat_vec(int(wv.tensor_type), np.ascontiguousarray(wv.data), nkv, E, xn)
+        kk = oracle.mul_mat_vec(int(wk.tensor_type), np.ascontiguousarray(wk.data), nkv, E, xn, faithful=2)
+        vv = oracle.mul_mat_vec(int(wv.tensor_type), np.ascontiguousarray(wv.data), nkv, E, xn, faithful=2)
         kk = oracle.rope(kk, m.info.n_head_kv, m.info.head_dim, m.info.n_rot, pos, om.m.rope_freq_base, 0)
-        assert np.max(np.abs(k[pos].astype(np.float32) - kk.astype(np.float16).astype(np.float32))) <= 2e-3
-        assert np.max(np.abs(v[pos].astype(np.float32) - vv.astype(np.float16).astype(np.float32))) <= 2e-3
+        assert np.array_equal(k[pos], kk.astype(np.float16))
+        assert np.array_equal(v[pos], vv.astype(np.float16))
     m.close()
 
 
