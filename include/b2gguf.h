@@ -122,6 +122,17 @@ int b2_dequantize_repacked(int ggml_type, const void* blocks, int64_t rows, int6
  * semantics.  gain (k floats, may be NULL) applies the fused RMSNorm prologue first:
  * x <- rms_norm(x, eps) * gain. */
 int b2_gemv(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, const float* gain, float eps, float* y);
+/* b2_gemv without any device allocation -- no counterpart in the reference (nor in b2_gemv's
+ * upstream analogue): it exists for callers that cannot call cudaMalloc, e.g. a server whose KV
+ * cache already fills the GPU, code living inside another framework's memory pool, or a path
+ * that cannot afford cudaMalloc's device-wide synchronisation.  All device staging lives in a
+ * static array of B2_NOALLOC_SCRATCH_BYTES inside the library (held on every GPU that loads it,
+ * until exit).  Same arguments and results as b2_gemv; matrices whose staging does not fit
+ * (roughly rows*k > 6.5 M weights for Q4_0) are rejected with B2_ERR_NOMEM.  The first call on a
+ * device resolves the array's address and should precede any stream capture.  Calls share the
+ * array: do not let two of them overlap on the GPU. */
+#define B2_NOALLOC_SCRATCH_BYTES (8u << 20)
+int b2_gemv_noalloc(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, const float* gain, float eps, float* y);
 /* Same kernel launched `iters` times back to back on resident data; returns the mean device
  * time per launch in *ms_out (CUDA events).  tune = {nb, g, rpg, ns, ctas_per_sm}, zeros for
  * the built-in heuristic. */
