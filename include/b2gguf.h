@@ -141,6 +141,9 @@ int b2_gemv_bench(int ggml_type, int64_t rows, int64_t k, int iters, const int* 
  * f16 (row-major, unpaged on the host side; the hook pages them) -> out[n_head*head_dim]. */
 int b2_attn_decode(const float* q, const uint16_t* k, const uint16_t* v, int n_ctx, int n_head, int n_head_kv,
                    int head_dim, float scale, int cluster, float* out);
+/* The attention kernel launched `iters` times back to back over `n_layers` distinct caches of n_ctx
+ * tokens (cluster = 0 for the built-in choice); mean device milliseconds per launch in *ms_out. */
+int b2_attn_bench(int n_ctx, int n_head, int n_head_kv, int head_dim, int cluster, int n_layers, int iters, float* ms_out);
 /* Read back one per-sequence activation buffer as it stands after the last step:
  * what = 0 residual stream x[n_embd], 1 rotated query q[n_head*head_dim], 2 attention output,
  * 3 FFN hidden h[n_ff], 4 logits[n_vocab], 5 phi-2 attention projection[n_embd]. */

@@ -317,4 +317,45 @@ int b2_attn_decode(const float* q, const uint16_t* k, const uint16_t* v, int n_c
     return B2_OK;
 }
 
+int b2_attn_bench(int n_ctx, int n_head, int n_head_kv, int head_dim, int cluster, int n_layers, int iters, float* ms_out) {
+    if (!ms_out || n_ctx <= 0 || iters <= 0 || n_layers <= 0) B2_FAIL(B2_ERR_ARG, "b2_attn_bench: bad arguments");
+    B2_TRY(check_device());
+    const size_t kvd = (size_t)n_head_kv * head_dim, nq = (size_t)n_head * head_dim;
+    const int n_pages = (n_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const size_t layer_elems = (size_t)n_pages * PAGE_TOKENS * kvd;
+    DevBuf dq, dk, dv, dout, dpt, dpos;
+    B2_TRY(dq.alloc(nq * 4)); B2_TRY(dout.alloc(nq * 4));
+    B2_TRY(dk.alloc(layer_elems * 2 * n_layers)); B2_TRY(dv.alloc(layer_elems * 2 * n_layers));
+    B2_TRY(dpt.alloc((size_t)n_pages * 4)); B2_TRY(dpos.alloc(4));
+    B2_CUDA(cudaMemset(dk.p, 0, layer_elems * 2 * n_layers)); B2_CUDA(cudaMemset(dv.p, 0, layer_elems * 2 * n_layers));
+    B2_CUDA(cudaMemset(dq.p, 0, nq * 4));
+    std::vector<int> pt(n_pages);
+    for (int i = 0; i < n_pages; i++) pt[i] = i;
+    const int pos = n_ctx - 1;
+    B2_CUDA(cudaMemcpy(dpt.p, pt.data(), (size_t)n_pages * 4, cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(dpos.p, &pos, 4, cudaMemcpyHostToDevice));
+    cudaStream_t st;
+    B2_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaEvent_t e0, e1;
+    B2_CUDA(cudaEventCreate(&e0)); B2_CUDA(cudaEventCreate(&e1));
+    int rc = B2_OK;
+    for (int pass = 0; pass < 2 && rc == B2_OK; pass++) {
+        const int n = pass == 0 ? std::min(iters, 3) : iters;
+        cudaEventRecord(e0, st);
+        for (int i = 0; i < n && rc == B2_OK; i++) {
+            AttnArgs a;
+            const int l = i % n_layers;        // a different layer's cache every launch, like the decode loop
+            a.q = dq.as<float>(); a.out = dout.as<float>(); a.k_base = dk.as<__half>() + layer_elems * l; a.v_base = dv.as<__half>() + layer_elems * l;
+            a.page_table = dpt.as<int>(); a.pos = dpos.as<int>(); a.n_head = n_head; a.n_head_kv = n_head_kv; a.head_dim = head_dim;
+            a.page_tokens = PAGE_TOKENS; a.kv_dim = (int)kvd; a.max_ctx = n_ctx; a.scale = 1.0f;
+            rc = attn_decode_launch(a, st, true, cluster);
+        }
+        cudaEventRecord(e1, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess && rc == B2_OK) { set_error("b2_attn_bench: %s", cudaGetErrorString(cudaGetLastError())); rc = B2_ERR_CUDA; }
+        if (pass == 1 && rc == B2_OK) { float ms = 0; cudaEventElapsedTime(&ms, e0, e1); *ms_out = ms / iters; }
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+    return rc;
+}
+
 }  // extern "C"

@@ -613,12 +613,14 @@ int gemv_launch(const GemvArgs& a, cudaStream_t st, bool pdl, const GemvTune* tu
     if (nb > 4) nb = 4;
     c.S = (c.nunits + 32 * nb - 1) / (32 * nb);
     if (c.S > 16) B2_FAIL(B2_ERR_UNSUPPORTED, "gemv: k=%lld too large", (long long)W.k);
-    const int ctas_per_sm = tune && tune->ctas_per_sm ? tune->ctas_per_sm : 2;
-    c.G = tune && tune->g ? tune->g : (c.S == 1 ? 4 : c.S == 2 ? 2 : c.S <= 4 ? 2 : 1);
+    // defaults from the round-1 sweep on B200 (profiles/r01a_gemv_sweep.txt): 8 consumer warps per
+    // CTA when a warp covers the whole row, two CTAs per SM; long rows take one bigger CTA per SM
+    const int ctas_per_sm = tune && tune->ctas_per_sm ? tune->ctas_per_sm : (c.S == 1 ? 2 : 1);
+    c.G = tune && tune->g ? tune->g : (c.S == 1 ? 8 : c.S <= 4 ? 4 : 2);
     const int max_cons = kq ? 8 : 16;      // bounded by the kernels' __launch_bounds__
     if (c.S > max_cons) B2_FAIL(B2_ERR_UNSUPPORTED, "gemv: k=%lld too large for type %d", (long long)W.k, W.type);
     if (c.G * c.S > max_cons) c.G = max(1, max_cons / c.S);
-    c.RPG = tune && tune->rpg ? (tune->rpg + 1) / 2 * 2 : 2;
+    c.RPG = tune && tune->rpg ? (tune->rpg + 1) / 2 * 2 : (c.S == 1 ? 2 : 4);
     c.RT = c.G * c.RPG;
     size_t row_bytes = 0;
     for (int p = 0; p < W.n_planes; p++) row_bytes += W.stride[p];
@@ -634,7 +636,7 @@ int gemv_launch(const GemvArgs& a, cudaStream_t st, bool pdl, const GemvTune* tu
     c.off_xs = (uint32_t)off; off += xs_bytes; off = (off + 127) / 128 * 128;
     c.off_stage = (uint32_t)off;
     const size_t budget = (size_t)(227 * 1024) / ctas_per_sm - 1024;   // 1 KB per CTA is reserved by the driver
-    int ns = tune && tune->ns ? tune->ns : 4;
+    int ns = tune && tune->ns ? tune->ns : (c.S == 1 ? 3 : 4);
     if (ns > MAX_NS) ns = MAX_NS;
     while (ns > 1 && off + (size_t)ns * c.stage_bytes > budget) ns--;
     if (off + (size_t)ns * c.stage_bytes > 227 * 1024) B2_FAIL(B2_ERR_UNSUPPORTED, "gemv: k=%lld does not fit shared memory", (long long)W.k);

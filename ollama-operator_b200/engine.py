@@ -22,7 +22,7 @@ LOAD_NO_PDL, LOAD_NO_GRAPH = 1, 2
 SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
     "b2_seq_new", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
-    "b2_get_stats", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_kv_read", "b2_debug_read",
+    "b2_get_stats", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
 ]
 
 
@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
         L.b2_gemv_noalloc.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp, vp, C.c_float, vp]
         L.b2_gemv_bench.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int, vp, fp]
         L.b2_attn_decode.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp]
+        L.b2_attn_bench.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, fp]
         L.b2_kv_read.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_int]
         L.b2_debug_read.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
         _lib = L
@@ -152,6 +153,13 @@ def attn_decode(q: np.ndarray, k: np.ndarray, v: np.ndarray, n_head: int, n_head
     out = np.empty(n_head * head_dim, dtype=np.float32)
     _check(lib().b2_attn_decode(_ptr(q), _ptr(k), _ptr(v), k.shape[0], n_head, n_head_kv, head_dim, scale, cluster, _ptr(out)))
     return out
+
+
+def attn_bench(n_ctx: int, n_head: int, n_head_kv: int, head_dim: int, cluster: int = 0, n_layers: int = 32, iters: int = 128) -> float:
+    """Mean device milliseconds per launch of the decode-attention kernel."""
+    ms = C.c_float(0)
+    _check(lib().b2_attn_bench(n_ctx, n_head, n_head_kv, head_dim, cluster, n_layers, iters, C.byref(ms)))
+    return ms.value
 
 
 # ---- engine -------------------------------------------------------------------------------------------

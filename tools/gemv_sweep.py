@@ -31,3 +31,11 @@ for name, t, rows, k in SHAPES:
     res.sort(key=lambda r: -r[0])
     for gbs, ms, tune in res[:6] + [r for r in res if r[2] is None]:
         print(f"{name:9s} {rows}x{k} tune={tune} {ms * 1e3:8.2f} us {gbs:8.1f} GB/s", flush=True)
+
+if not only or "attn" in only:
+    for (nh, nkv, hd) in [(32, 32, 128), (32, 8, 128), (64, 8, 128)]:
+        for ctx in (128, 512, 2048):
+            for cl in (1, 2, 4, 8):
+                ms = E.attn_bench(ctx, nh, nkv, hd, cl)
+                kvb = ctx * nkv * hd * 4
+                print(f"attn heads {nh}/{nkv} hd {hd} ctx {ctx:5d} cluster {cl}: {ms * 1e3:8.2f} us  {kvb / ms / 1e6:8.1f} GB/s", flush=True)
