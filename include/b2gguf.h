@@ -52,7 +52,8 @@ typedef struct {
     int32_t flags;       /* B2_LOAD_* */
 } b2_load_opts;
 enum { B2_LOAD_NO_PDL = 1,      /* do not use programmatic dependent launch */
-       B2_LOAD_NO_GRAPH = 2 };  /* launch kernels one by one instead of replaying CUDA graphs */
+       B2_LOAD_NO_GRAPH = 2,    /* launch kernels one by one instead of replaying CUDA graphs */
+       B2_LOAD_NO_MEGA = 4 };   /* one kernel per matrix instead of the persistent per-step kernel */
 
 typedef struct {
     int32_t arch;        /* 0 llama, 1 phi2 */

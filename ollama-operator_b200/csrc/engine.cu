@@ -67,6 +67,7 @@ Model::~Model() {
     for (auto& s : slots) {
         if (s.g_full) cudaGraphExecDestroy(s.g_full);
         if (s.g_nohead) cudaGraphExecDestroy(s.g_nohead);
+        if (s.d_stages) cudaFree(s.d_stages);
     }
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
@@ -178,6 +179,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
     const int flags = o ? o->flags : 0;
     use_pdl = !(flags & B2_LOAD_NO_PDL) && !getenv("B2_NO_PDL");
     use_graph = !(flags & B2_LOAD_NO_GRAPH) && !getenv("B2_NO_GRAPH");
+    use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
 
     const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd, F = hp.n_ff, V = hp.n_vocab;
     if ((nq | nkv | F | V | E) & 1) B2_FAIL(B2_ERR_UNSUPPORTED, "odd matrix dimensions are not supported");
@@ -321,7 +323,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
     auto carve = [&](size_t bytes) { const size_t o2 = align_up(off, 256); off = o2 + bytes; return o2; };
     const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
                  o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
-                 o_pos = carve(4), o_key = carve(8), o_out = carve((size_t)out_cap * 4),
+                 o_pos = carve(4), o_key = carve(8), o_gc = carve(4), o_out = carve((size_t)out_cap * 4),
                  o_forced = carve((size_t)max_ctx * 4);
     const size_t slot_bytes = align_up(off, 256);
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
@@ -333,7 +335,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
         s.d_state = (SeqState*)(b + o_state); s.d_page_table = (int*)(b + o_pt); s.x = (float*)(b + o_x); s.q = (float*)(b + o_q);
         s.att = (float*)(b + o_att); s.att2 = (float*)(b + o_att2); s.h = (float*)(b + o_h); s.logits = (float*)(b + o_logits);
         s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
-        s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced);
+        s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced); s.d_grid_count = (unsigned*)(b + o_gc);
     }
     // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (theta starts
     // at pos and is multiplied by freq_base^(-2/n_rot) once per pair; libm cosf/sinf)
@@ -350,6 +352,10 @@ int Model::load(const char* path, const b2_load_opts* o) {
         }
         B2_CUDA(cudaMalloc(&rope_table, tab.size() * sizeof(float2)));
         B2_CUDA(cudaMemcpy(rope_table, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    }
+    for (Slot& s : slots) {
+        build_ops(s);
+        B2_TRY(setup_mega(s));
     }
     return B2_OK;
 }
@@ -405,6 +411,95 @@ int Model::ensure_pages(Slot& s, int upto) {
     return B2_OK;
 }
 
+// ---- the layer pipeline of one sequence slot: 5 ops per layer (qkv may be split by tensor type) -----
+void Model::build_ops(Slot& s) {
+    const int hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd;
+    s.ops.clear();
+    for (int l = 0; l < hp.n_layer; l++) {
+        const LayerW& L = layers[l];
+        __half* kb = kv_k + layer_kv_elems * l;
+        __half* vb = kv_v + layer_kv_elems * l;
+        for (const QkvSeg& seg : L.qkv) {
+            StepOp op; op.kind = 0; op.cls = 1;
+            GemvArgs& a = op.g;
+            a.W = seg.W; a.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; a.epi = EPI_QKV_ROPE;
+            a.x = s.x; a.gain = L.attn_norm; a.nbias = L.attn_norm_b; a.eps = hp.norm_eps;
+            a.bias = L.b_qkv; a.y = s.q; a.epi_row0 = seg.row0;
+            a.n_q = nq; a.n_kv = nkv; a.head_dim = hd; a.n_rot = hp.n_rot; a.rope_neox = neox ? 1 : 0;
+            a.q_scale = hp.arch == 1 ? 1.0f / sqrtf((float)hd) : 1.0f;
+            a.rope_cs = rope_table;
+            a.kv.k_base = kb; a.kv.v_base = vb; a.kv.page_table = s.d_page_table; a.kv.pos = s.d_pos;
+            a.kv.page_tokens = PAGE_TOKENS; a.kv.kv_dim = nkv;
+            s.ops.push_back(op);
+        }
+        {
+            StepOp op; op.kind = 1; op.cls = 2;
+            AttnArgs& a = op.a;
+            a.q = s.q; a.out = s.att; a.k_base = kb; a.v_base = vb; a.page_table = s.d_page_table; a.pos = s.d_pos;
+            a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.head_dim = hd; a.page_tokens = PAGE_TOKENS; a.kv_dim = nkv;
+            a.max_ctx = max_ctx;
+            a.scale = hp.arch == 1 ? 1.0f : 1.0f / sqrtf((float)hd);
+            s.ops.push_back(op);
+        }
+        StepOp o, u, d;
+        o.kind = u.kind = d.kind = 0; o.cls = 3; u.cls = 4; d.cls = 5;
+        if (hp.arch == 0) {
+            o.g.W = L.w_o; o.g.pro = PRO_PLAIN; o.g.epi = EPI_RESIDUAL; o.g.x = s.att; o.g.y = s.x;
+            u.g.W = L.w_up; u.g.pro = PRO_RMSNORM; u.g.epi = EPI_SILU_MUL; u.g.x = s.x; u.g.gain = L.ffn_norm; u.g.eps = hp.norm_eps; u.g.y = s.h;
+            d.g.W = L.w_down; d.g.pro = PRO_PLAIN; d.g.epi = EPI_RESIDUAL; d.g.x = s.h; d.g.y = s.x;
+        } else {
+            o.g.W = L.w_o; o.g.pro = PRO_PLAIN; o.g.epi = EPI_STORE; o.g.x = s.att; o.g.bias = L.b_o; o.g.y = s.att2;
+            u.g.W = L.w_up; u.g.pro = PRO_LAYERNORM; u.g.epi = EPI_GELU; u.g.x = s.x; u.g.gain = L.attn_norm; u.g.nbias = L.attn_norm_b;
+            u.g.eps = hp.norm_eps; u.g.bias = L.b_up; u.g.y = s.h;
+            d.g.W = L.w_down; d.g.pro = PRO_PLAIN; d.g.epi = EPI_RESIDUAL2; d.g.x = s.h; d.g.bias = L.b_down; d.g.y = s.x; d.g.y2 = s.att2;
+        }
+        s.ops.push_back(o); s.ops.push_back(u); s.ops.push_back(d);
+    }
+}
+
+// Persistent-kernel path: possible when every layer matrix has the same supported type.
+int Model::setup_mega(Slot& s) {
+    s.mega_ok = false;
+    if (!use_mega) return B2_OK;
+    int type = -1;
+    for (const StepOp& op : s.ops)
+        if (op.kind == 0) {
+            if (type < 0) type = op.g.W.type;
+            if (op.g.W.type != type) return B2_OK;          // mixed tensor types: per-matrix kernels
+        }
+    const int grp = hp.n_head / hp.n_head_kv;
+    if (!mega_supported(type, grp, hp.head_dim)) return B2_OK;
+    std::vector<MegaStage> st(s.ops.size());
+    int64_t k_max = 0;
+    size_t tile_max = 0;
+    int rt_s_max = 0;
+    MegaLaunch& L = s.mega;
+    L = MegaLaunch();
+    L.type = type; L.grp = grp; L.head_dim = hp.head_dim; L.cluster = 4;
+    for (size_t i = 0; i < s.ops.size(); i++) {
+        st[i].kind = s.ops[i].kind;
+        if (s.ops[i].kind == 0) {
+            st[i].g = s.ops[i].g;
+            if (mega_plan_stage(st[i], MEGA_NCW) != B2_OK) return B2_OK;
+            const QMat& W = st[i].g.W;
+            size_t rb = 0;
+            for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
+            k_max = std::max(k_max, W.k);
+            tile_max = std::max(tile_max, rb * st[i].RT);
+            rt_s_max = std::max(rt_s_max, st[i].RT * st[i].S);
+        } else {
+            st[i].at = s.ops[i].a;
+        }
+    }
+    if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) return B2_OK;     // does not fit: keep the per-matrix path
+    for (auto& x : st) x.att_max_local = L.att_max_local;
+    B2_CUDA(cudaMalloc(&s.d_stages, st.size() * sizeof(MegaStage)));
+    B2_CUDA(cudaMemcpy(s.d_stages, st.data(), st.size() * sizeof(MegaStage), cudaMemcpyHostToDevice));
+    L.stages = s.d_stages; L.s_begin = 0; L.s_end = (int)st.size(); L.grid_count = s.d_grid_count;
+    s.mega_ok = true;
+    return B2_OK;
+}
+
 // ---- one decode step, as a chain of kernel launches on `stream` -----------------------------------
 int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof) {
     auto mark = [&](int cls) -> int {
@@ -417,66 +512,28 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
         return B2_OK;
     };
     B2_TRY(mark(-1));
-    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd;
     int nl = 0;
     const bool pdl = use_pdl;
     {
         StepBeginArgs a;
-        a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key;
+        a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key; a.grid_count = s.d_grid_count;
         B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
     }
-    for (int l = 0; l < hp.n_layer; l++) {
-        const LayerW& L = layers[l];
-        __half* kb = kv_k + layer_kv_elems * l;
-        __half* vb = kv_v + layer_kv_elems * l;
-        for (const QkvSeg& seg : L.qkv) {
-            GemvArgs a;
-            a.W = seg.W; a.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; a.epi = EPI_QKV_ROPE;
-            a.x = s.x; a.gain = L.attn_norm; a.nbias = L.attn_norm_b; a.eps = hp.norm_eps;
-            a.bias = L.b_qkv; a.y = s.q; a.epi_row0 = seg.row0;
-            a.n_q = nq; a.n_kv = nkv; a.head_dim = hd; a.n_rot = hp.n_rot; a.rope_neox = neox ? 1 : 0;
-            a.q_scale = hp.arch == 1 ? 1.0f / sqrtf((float)hd) : 1.0f;
-            a.rope_cs = rope_table;
-            a.kv.k_base = kb; a.kv.v_base = vb; a.kv.page_table = s.d_page_table; a.kv.pos = s.d_pos;
-            a.kv.page_tokens = PAGE_TOKENS; a.kv.kv_dim = nkv;
-            B2_TRY(gemv_launch(a, stream, pdl)); nl++; B2_TRY(mark(1));
-        }
-        {
-            AttnArgs a;
-            a.q = s.q; a.out = s.att; a.k_base = kb; a.v_base = vb; a.page_table = s.d_page_table; a.pos = s.d_pos;
-            a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.head_dim = hd; a.page_tokens = PAGE_TOKENS; a.kv_dim = nkv;
-            a.max_ctx = max_ctx;
-            a.scale = hp.arch == 1 ? 1.0f : 1.0f / sqrtf((float)hd);
-            B2_TRY(attn_decode_launch(a, stream, pdl)); nl++; B2_TRY(mark(2));
-        }
-        if (hp.arch == 0) {
-            GemvArgs o;
-            o.W = L.w_o; o.pro = PRO_PLAIN; o.epi = EPI_RESIDUAL; o.x = s.att; o.y = s.x;
-            B2_TRY(gemv_launch(o, stream, pdl)); nl++; B2_TRY(mark(3));
-            GemvArgs u;
-            u.W = L.w_up; u.pro = PRO_RMSNORM; u.epi = EPI_SILU_MUL; u.x = s.x; u.gain = L.ffn_norm; u.eps = hp.norm_eps; u.y = s.h;
-            B2_TRY(gemv_launch(u, stream, pdl)); nl++; B2_TRY(mark(4));
-            GemvArgs d;
-            d.W = L.w_down; d.pro = PRO_PLAIN; d.epi = EPI_RESIDUAL; d.x = s.h; d.y = s.x;
-            B2_TRY(gemv_launch(d, stream, pdl)); nl++; B2_TRY(mark(5));
-        } else {
-            GemvArgs o;
-            o.W = L.w_o; o.pro = PRO_PLAIN; o.epi = EPI_STORE; o.x = s.att; o.bias = L.b_o; o.y = s.att2;
-            B2_TRY(gemv_launch(o, stream, pdl)); nl++; B2_TRY(mark(3));
-            GemvArgs u;
-            u.W = L.w_up; u.pro = PRO_LAYERNORM; u.epi = EPI_GELU; u.x = s.x; u.gain = L.attn_norm; u.nbias = L.attn_norm_b;
-            u.eps = hp.norm_eps; u.bias = L.b_up; u.y = s.h;
-            B2_TRY(gemv_launch(u, stream, pdl)); nl++; B2_TRY(mark(4));
-            GemvArgs d;
-            d.W = L.w_down; d.pro = PRO_PLAIN; d.epi = EPI_RESIDUAL2; d.x = s.h; d.bias = L.b_down; d.y = s.x; d.y2 = s.att2;
-            B2_TRY(gemv_launch(d, stream, pdl)); nl++; B2_TRY(mark(5));
+    if (s.mega_ok && !prof) {
+        B2_TRY(mega_launch(s.mega, stream)); nl++;
+    } else {
+        for (const StepOp& op : s.ops) {
+            if (op.kind == 0) B2_TRY(gemv_launch(op.g, stream, pdl));
+            else B2_TRY(attn_decode_launch(op.a, stream, pdl));
+            nl++;
+            B2_TRY(mark(op.cls));
         }
     }
     if (with_head) {
         GemvArgs h;
         h.W = w_head; h.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; h.epi = EPI_LOGITS;
         h.x = s.x; h.gain = out_norm; h.nbias = out_norm_b; h.eps = hp.norm_eps; h.bias = head_b; h.y = s.logits; h.argmax_key = s.d_key;
-        B2_TRY(gemv_launch(h, stream, pdl)); nl++; B2_TRY(mark(6));
+        B2_TRY(gemv_launch(h, stream, pdl && !s.mega_ok)); nl++; B2_TRY(mark(6));
     }
     {
         StepEndArgs a;

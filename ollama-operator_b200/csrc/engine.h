@@ -36,6 +36,8 @@ struct LayerW {
     float *b_qkv = nullptr, *b_o = nullptr, *b_up = nullptr, *b_down = nullptr;
 };
 
+struct StepOp { int kind = 0; int cls = 0; GemvArgs g; AttnArgs a; };     // kind 0 = GEMV, 1 = attention
+
 struct Slot {
     bool used = false;
     int len = 0;                   // tokens in the KV cache
@@ -48,6 +50,11 @@ struct Slot {
     int* d_pos = nullptr;
     unsigned long long* d_key = nullptr;
     int *d_out = nullptr, *d_forced = nullptr;
+    unsigned* d_grid_count = nullptr;
+    std::vector<StepOp> ops;       // the layer pipeline with this slot's buffers bound
+    bool mega_ok = false;          // the persistent kernel can run this model
+    MegaLaunch mega;
+    MegaStage* d_stages = nullptr;
     cudaGraphExec_t g_full = nullptr, g_nohead = nullptr;
     int gl_full = 0, gl_nohead = 0;
     bool warm_full = false, warm_nohead = false;
@@ -57,7 +64,7 @@ struct StepProfile { std::vector<cudaEvent_t> ev; std::vector<int> cls; };
 
 struct Model {
     HParams hp;
-    bool neox = false, use_pdl = true, use_graph = true;
+    bool neox = false, use_pdl = true, use_graph = true, use_mega = true;
     int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
     float2* rope_table = nullptr;     // [max_ctx][n_rot/2]
     Arena arena;
@@ -92,6 +99,8 @@ struct Model {
     int upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step, int64_t src_row0);
     int upload_f32(const GgufFile& f, const std::string& name, int64_t n, float** out, bool optional);
     int upload_rows_headwise(const GgufTensor* t, int64_t n_heads, int64_t k, const QMat& dst, int64_t dst_row0, int64_t src_row0);
+    void build_ops(Slot& s);
+    int setup_mega(Slot& s);
     int ensure_pages(Slot& s, int upto);
     int enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof);
     int run_steps(Slot& s, bool with_head, int n);

@@ -73,6 +73,33 @@ struct AttnArgs {
 };
 int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster = 0);
 
+// ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
+constexpr int MEGA_NCW = 16;      // consumer warps per CTA
+struct MegaStage {                // one stage of the layer pipeline, resident in device memory
+    int kind = 0;                 // 0 = GEMV, 1 = attention
+    GemvArgs g;
+    int S = 1;                    // warps along K per row
+    int P = 2;                    // warps sharing a row pair (each takes every P-th row)
+    int G = 1;                    // row groups per CTA (G * S * P <= MEGA_NCW)
+    int RPG = 2, RT = 2;          // rows per group per tile, rows per tile
+    int nunits = 0, nbeff = 4;    // units per row, units per lane actually used
+    AttnArgs at;
+    int att_max_local = 0;
+};
+struct MegaLaunch {
+    const MegaStage* stages = nullptr;   // device array
+    int s_begin = 0, s_end = 0;
+    unsigned* grid_count = nullptr;      // zeroed before every launch
+    int type = 0, grp = 1, head_dim = 0, cluster = 4, grid = 0;
+    uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
+    int ns = 0, att_max_local = 0;
+    size_t smem_bytes = 0;
+};
+bool mega_supported(int type, int grp, int head_dim);
+int mega_plan_stage(MegaStage& st, int ncw);
+int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);
+int mega_launch(const MegaLaunch& L, cudaStream_t stream);
+
 // ---- step.cu: per-step bookkeeping kernels ----------------------------------------------------
 struct SeqState {        // one per sequence slot, resident on the device
     int pos;             // position of the token about to be evaluated
@@ -88,6 +115,7 @@ struct StepBeginArgs {
     float* x = nullptr;            // [n_embd]
     int* pos_out = nullptr;        // device scalar consumed by the layer kernels
     unsigned long long* argmax_key = nullptr;
+    unsigned* grid_count = nullptr;   // persistent kernel's barrier counter, cleared every step (may be null)
 };
 int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
 struct StepEndArgs {

@@ -20,6 +20,7 @@ __global__ void step_begin_kernel(const StepBeginArgs a) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *a.pos_out = pos;
         *a.argmax_key = 0ull;
+        if (a.grid_count) *a.grid_count = 0u;
     }
 }
 
