@@ -108,6 +108,11 @@ int b2_decode(b2_model* m, int n_seq, const int* seqs, const int32_t* last_tok, 
 int b2_decode_greedy(b2_model* m, int seq, int32_t first_tok, int n_steps, int32_t* out_toks);
 
 int b2_get_stats(const b2_model* m, b2_stats* out);
+/* One decode step through the persistent per-step kernel with time stamps: out receives
+ * [n_cta][n_stage][12] GPU-global nanosecond stamps {stage entered, grid barrier passed, prologue
+ * done, stage done, then eight phase stamps of the attention stage} (stages: per layer qkv,
+ * attention, wo, gate|up, down).  Tuning aid. */
+int b2_mega_trace(b2_model* m, int seq, int32_t tok, uint64_t* out, int cap, int* n_cta, int* n_stage);
 /* One decode step for `seq` (like b2_decode with one sequence) run with a CUDA event after every
  * kernel: class_ms[8] / class_launches[8] receive device milliseconds and launch counts per
  * kernel class {0 step-begin, 1 qkv gemv, 2 attention, 3 wo gemv, 4 gate/up gemv, 5 down gemv,

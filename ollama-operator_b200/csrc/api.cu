@@ -166,6 +166,10 @@ int b2_debug_read(b2_model* m, int seq, int what, float* out, int n) {
     B2_CUDA(cudaMemcpy(out, src, (size_t)n * 4, cudaMemcpyDeviceToHost));
     return B2_OK;
 }
+int b2_mega_trace(b2_model* m, int seq, int32_t tok, uint64_t* out, int cap, int* n_cta, int* n_stage) {
+    if (!n_cta || !n_stage) B2_FAIL(B2_ERR_ARG, "b2_mega_trace: null argument");
+    B2_MODEL_CALL(m, m->m.mega_trace(seq, tok, (unsigned long long*)out, cap, n_cta, n_stage));
+}
 int b2_get_stats(const b2_model* m, b2_stats* out) {
     if (!m || !out) B2_FAIL(B2_ERR_ARG, "b2_get_stats: null argument");
     out->steps = m->m.steps; out->kernel_launches = m->m.launches; out->gpu_ms = m->m.last_ms;

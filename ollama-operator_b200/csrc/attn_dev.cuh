@@ -51,8 +51,11 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // same shared-memory offset in every CTA), `xphase` its running phase; `barid` a CTA-local named
 // barrier covering exactly the NT callers.
 template <int GRP, int HD, int NT>
-static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh, uint8_t* smem_raw, int tid, uint64_t* xb, uint32_t& xphase,
-                                    int barid) {
+static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh, uint8_t* smem_raw, int tid, uint64_t* xb, uint32_t& xphase,
+                                    int barid, int pos_value = -1, const int* page_table_override = nullptr,
+                                    unsigned long long* tr = nullptr) {
+    auto stamp = [&](int k) { if (tr) { unsigned long long tt; tt = (unsigned long long)clock64(); tr[k] = tt; } };
+    stamp(0);
     constexpr int ATT_THREADS = NT, ATT_WARPS = NT / 32;
     const int lane = tid & 31, warp = tid >> 5;
     const uint32_t rk = cluster_ctarank();
@@ -68,14 +71,16 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
     double* merge = ored + (size_t)npl * GRP * HD;                  // rank 0 only: [cluster][GRP][HD]
     double* csum = merge + (size_t)c.cluster * GRP * HD;            // [MAX_CLUSTER][GRP] every CTA's sum (all-gathered)
     double* wsum = csum + MAX_CLUSTER * GRP;                        // [ATT_WARPS][GRP] cross-warp scratch
-    uint4* vbuf = reinterpret_cast<uint4*>(wsum + ATT_WARPS * GRP); // [2][VCH][ROW16] V chunks (cp.async)
+    uint4* vbuf = reinterpret_cast<uint4*>(wsum + (ATT_WARPS * GRP + 1) / 2 * 2); // [2][VCH][ROW16] V chunks (cp.async), 16-byte aligned
     float* qs = reinterpret_cast<float*>(vbuf + 2 * VCH * ROW16);   // [GRP][HD]   f16-rounded query
     float* sc = qs + GRP * HD;                                      // [GRP][max_local] scores -> probabilities
     float* wred = sc + (size_t)GRP * c.max_local;                   // [ATT_WARPS][GRP] cross-warp scratch
     float* ml = wred + ATT_WARPS * GRP;                             // [2][GRP] global max, 1/sum
     float* cmax = ml + 2 * GRP;                                     // [MAX_CLUSTER][GRP] every CTA's max (all-gathered)
 
-    const int n = *a.pos + 1;
+    // position and page table: the persistent kernel hands in copies it made once per step
+    const int* page_table = page_table_override ? page_table_override : a.page_table;
+    const int n = (pos_value >= 0 ? pos_value : *a.pos) + 1;
     const int per = (n + c.cluster - 1) / c.cluster;
     const int t_begin = min(n, (int)rk * per), t_end = min(n, t_begin + per);
     const int n_loc = t_end - t_begin;
@@ -88,7 +93,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
             const int t0 = t_begin + ch * VCH, cnt = min(VCH, t_end - t0);
             for (int i = tid; i < cnt * ROW16; i += ATT_THREADS) {
                 const int t = t0 + i / ROW16;
-                const int page = a.page_table[t / a.page_tokens];
+                const int page = page_table[t / a.page_tokens];
                 const __half* src = a.v_base + ((size_t)page * a.page_tokens + t % a.page_tokens) * a.kv_dim + (size_t)kvh * HD + (i % ROW16) * 8;
                 cp_async16(dst + i, src);
             }
@@ -98,31 +103,40 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
     issue_v_chunk(0);
     issue_v_chunk(1);
 
-    for (int i = tid; i < GRP * HD; i += ATT_THREADS)
-        qs[i] = __half2float(__float2half_rn(a.q[(size_t)kvh * GRP * HD + i]));
-    named_bar_sync(barid, NT);
-
     // ---- phase 1: scores.  Two threads share a cached position (half of the dims each).  f16 x f16
     //      products are exact in f32 and are added in f64 (as ggml's scalar f16 dot does), so neither
-    //      the split nor the four partial sums per thread change the result. ----------------------------
+    //      the split nor the four partial sums per thread change the result.  The K rows of the first
+    //      round are requested before the query is staged, so both latencies overlap. -------------------
     constexpr int HALF16 = ROW16 / 2;          // 16-byte pieces per thread
+    const int hsel = tid & 1;
+    uint4 kreg[HALF16];
+    auto load_k = [&](int i) {
+        if (i < n_loc) {
+            const int t = t_begin + i;
+            const int page = page_table[t / a.page_tokens];
+            const uint4* kr = reinterpret_cast<const uint4*>(a.k_base + ((size_t)page * a.page_tokens + t % a.page_tokens) * a.kv_dim +
+                                                             (size_t)kvh * HD) + hsel * HALF16;
+#pragma unroll
+            for (int ch = 0; ch < HALF16; ch++) kreg[ch] = kr[ch];
+        }
+    };
+    load_k(tid >> 1);
+    for (int i = tid; i < GRP * HD; i += ATT_THREADS)
+        qs[i] = __half2float(__float2half_rn(__ldcg(a.q + (size_t)kvh * GRP * HD + i)));
+    named_bar_sync(barid, NT);
+    stamp(1);
+
     float lmax[GRP];
 #pragma unroll
     for (int g = 0; g < GRP; g++) lmax[g] = -INFINITY;
     for (int base = 0; base < n_loc; base += ATT_THREADS / 2) {
-        const int i = base + (tid >> 1), hsel = tid & 1;
+        const int i = base + (tid >> 1);
         const bool active = i < n_loc;
+        if (base > 0) load_k(i);
         double s[GRP];
 #pragma unroll
         for (int g = 0; g < GRP; g++) s[g] = 0.0;
         if (active) {
-            const int t = t_begin + i;
-            const int page = a.page_table[t / a.page_tokens];
-            const uint4* kr = reinterpret_cast<const uint4*>(a.k_base + ((size_t)page * a.page_tokens + t % a.page_tokens) * a.kv_dim +
-                                                             (size_t)kvh * HD) + hsel * HALF16;
-            uint4 kreg[HALF16];
-#pragma unroll
-            for (int ch = 0; ch < HALF16; ch++) kreg[ch] = kr[ch];
             double part[GRP][4];
 #pragma unroll
             for (int g = 0; g < GRP; g++)
@@ -157,6 +171,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
             }
         }
     }
+    stamp(2);
 #pragma unroll
     for (int g = 0; g < GRP; g++) {
         const float m = warp_max(lmax[g]);
@@ -179,6 +194,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
     }
     named_bar_sync(barid, NT);
 
+    stamp(3);
     // ---- phase 2: e = exp(s - max) rounded from f64, f64 sum, p = f16(e * (1/sum)) -------------------
     double lsum[GRP];
 #pragma unroll
@@ -204,6 +220,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
         dsmem_st_f64(dsmem_addr(csum + rk * GRP + g, r), sacc);
     }
     cluster_exchange(xb, xphase, c.cluster, tid, barid, NT);
+    stamp(4);
     if (tid < GRP) {
         double S = 0;
         for (int r = 0; r < c.cluster; r++) S += csum[r * GRP + tid];
@@ -216,6 +233,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
     }
     named_bar_sync(barid, NT);
 
+    stamp(5);
     // ---- phase 3: o = sum_t V_t * p_t (exact f32 products, f64 sum) from the shared-memory chunks;
     //      thread = (DW-wide dim group, position lane) -------------------------------------------------
     {
@@ -262,6 +280,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
     cp_async_wait<0>();
     named_bar_sync(barid, NT);
 
+    stamp(6);
     // ---- partial outputs of this slice -> rank 0 through DSMEM, summed there (f64) -------------------
     for (int i = tid; i < GRP * HD; i += ATT_THREADS) {
         const int g = i / HD, d = i % HD;
@@ -270,6 +289,7 @@ static __device__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh
         dsmem_st_f64(dsmem_addr(merge + ((size_t)rk * GRP + g) * HD + d, 0), o);
     }
     cluster_exchange(xb, xphase, c.cluster, tid, barid, NT);
+    stamp(7);
     if (rk != 0) return;
     for (int i = tid; i < GRP * HD; i += ATT_THREADS) {
         const int g = i / HD, d = i % HD;
@@ -284,7 +304,7 @@ static inline size_t attn_smem_bytes(int grp, int hd, int max_local, int cluster
     const int dw = grp <= 2 ? 8 : grp == 4 ? 4 : 2;
     const int ntv = nthreads < 256 ? nthreads : 256;
     const int ndg = hd / dw, npl = ntv / ndg, nwarps = nthreads / 32;
-    const size_t d = (size_t)npl * grp * hd + (size_t)cluster * grp * hd + MAX_CLUSTER * grp + (size_t)nwarps * grp;   // doubles
+    const size_t d = (size_t)npl * grp * hd + (size_t)cluster * grp * hd + MAX_CLUSTER * grp + (size_t)(nwarps * grp + 1) / 2 * 2;   // doubles (even count: what follows needs 16-byte alignment)
     const size_t v = (size_t)2 * VCH * (hd / 8) * 16;                                                                   // V chunks
     const size_t f = (size_t)grp * hd + (size_t)grp * max_local + (size_t)nwarps * grp + 2 * grp + MAX_CLUSTER * grp;   // floats
     return (d * sizeof(double) + v + f * sizeof(float) + 15) / 16 * 16;

@@ -486,16 +486,23 @@ int Model::setup_mega(Slot& s) {
             for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
             k_max = std::max(k_max, W.k);
             tile_max = std::max(tile_max, rb * st[i].RT);
-            rt_s_max = std::max(rt_s_max, st[i].RT * st[i].S);
+            // per-CTA row-sum buffer: (rows of the CTA + slack) x S doubles; sized for the smallest grid we might get
+            rt_s_max = std::max(rt_s_max, (int)((W.rows / 64 + 4) * st[i].S));
         } else {
             st[i].at = s.ops[i].a;
         }
     }
-    if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) return B2_OK;     // does not fit: keep the per-matrix path
+    if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) {
+        cudaGetLastError();          // does not fit: keep the per-matrix path, and leave no stale CUDA error behind
+        return B2_OK;
+    }
     for (auto& x : st) x.att_max_local = L.att_max_local;
     B2_CUDA(cudaMalloc(&s.d_stages, st.size() * sizeof(MegaStage)));
     B2_CUDA(cudaMemcpy(s.d_stages, st.data(), st.size() * sizeof(MegaStage), cudaMemcpyHostToDevice));
     L.stages = s.d_stages; L.s_begin = 0; L.s_end = (int)st.size(); L.grid_count = s.d_grid_count;
+    L.pos = s.d_pos; L.page_table = s.d_page_table; L.n_pages = pages_per_seq;
+    if (const char* v = getenv("B2_MEGA_INFLIGHT")) L.inflight = atoi(v);
+    if (pages_per_seq > 256) return B2_OK;          // the kernel keeps the page table in shared memory
     s.mega_ok = true;
     return B2_OK;
 }
@@ -691,6 +698,34 @@ int Model::profile_step(int seq, int32_t tok, float* class_ms, int* class_launch
             class_launches[prof.cls[i]]++;
         }
     for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
+    B2_TRY(rc);
+    B2_CUDA(cudaMemcpy(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost));
+    s.len += 1; steps += 1; launches += nl;
+    return B2_OK;
+}
+
+// One eager decode step through the persistent kernel with per-CTA, per-stage time stamps.
+int Model::mega_trace(int seq, int32_t tok, unsigned long long* out, int cap, int* n_cta, int* n_stage) {
+    B2_TRY(check_seq(seq));
+    Slot& s = slots[seq];
+    if (!s.mega_ok) B2_FAIL(B2_ERR_STATE, "mega_trace: the persistent kernel is not in use for this model");
+    const int nst = s.mega.s_end - s.mega.s_begin, ncta = s.mega.grid;
+    *n_cta = ncta; *n_stage = nst;
+    if (!out || cap < ncta * nst * 12) B2_FAIL(B2_ERR_ARG, "mega_trace: need room for %d values", ncta * nst * 12);
+    B2_TRY(ensure_pages(s, s.len + 1));
+    unsigned long long* d_tr = nullptr;
+    B2_CUDA(cudaMalloc(&d_tr, (size_t)ncta * nst * 12 * 8));
+    B2_CUDA(cudaMemset(d_tr, 0, (size_t)ncta * nst * 12 * 8));
+    SeqState st{};
+    st.pos = s.len; st.cur_tok = tok;
+    B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
+    s.mega.trace = d_tr;
+    int nl = 0;
+    const int rc = enqueue_step(s, true, &nl, nullptr);
+    s.mega.trace = nullptr;
+    cudaStreamSynchronize(stream);
+    if (rc == B2_OK) cudaMemcpy(out, d_tr, (size_t)ncta * nst * 12 * 8, cudaMemcpyDeviceToHost);
+    cudaFree(d_tr);
     B2_TRY(rc);
     B2_CUDA(cudaMemcpy(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost));
     s.len += 1; steps += 1; launches += nl;

@@ -94,6 +94,7 @@ struct Model {
     int decode_greedy(int seq, int32_t first_tok, int n_steps, int32_t* out_toks);
     int kv_read(int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok);
     int profile_step(int seq, int32_t tok, float* class_ms, int* class_launches);
+    int mega_trace(int seq, int32_t tok, unsigned long long* out, int cap, int* n_cta, int* n_stage);
 
   private:
     int upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step, int64_t src_row0);

@@ -242,18 +242,27 @@ struct RowPtrs { const uint8_t* p[4]; };
 
 __device__ __forceinline__ uint32_t u4c(const uint4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
-// ggml_vec_dot_q4_0_q8_0: sumf += sumi * d_w * d_a, sumi exact
+// unsigned-by-signed byte dot (dp4a.u32.s32): d = c + sum_i a.u8[i] * b.s8[i]
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// ggml_vec_dot_q4_0_q8_0: sumf += sumi * d_w * d_a, sumi exact.  The high nibbles are used in
+// place (w & 0xF0F0F0F0, as unsigned bytes = 16 * nibble): their dot is an exact multiple of 16,
+// so one shift at the end replaces four; the two accumulators also halve the dp4a dependency chain.
 __device__ __forceinline__ float unit_dot(const XRegs<T_Q4_0>& x, const RowPtrs& r, int u, int) {
     const uint4 w = *reinterpret_cast<const uint4*>(r.p[0] + u * 16);
     const float dw = h2f(*reinterpret_cast<const __half*>(r.p[1] + u * 2));
-    int s = 0;
+    int lo = 0, hi = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         const uint32_t ww = u4c(w, i);
-        s = __dp4a((int)(ww & 0x0F0F0F0Fu), (int)u4c(x.a, i), s);
-        s = __dp4a((int)((ww >> 4) & 0x0F0F0F0Fu), (int)u4c(x.b, i), s);
+        lo = __dp4a((int)(ww & 0x0F0F0F0Fu), (int)u4c(x.a, i), lo);
+        hi = dp4a_us(ww & 0xF0F0F0F0u, (int)u4c(x.b, i), hi);
     }
-    return __fmul_rn(__fmul_rn((float)(s - x.s8), dw), x.d);
+    return __fmul_rn(__fmul_rn((float)(lo + (hi >> 4) - x.s8), dw), x.d);
 }
 // ggml_vec_dot_q8_0_q8_0: sumf += sumi * (d_w * d_a); plane0 is chunk-interleaved [2][nunits][16]
 __device__ __forceinline__ float unit_dot(const XRegs<T_Q8_0>& x, const RowPtrs& r, int u, int nunits) {
@@ -356,7 +365,8 @@ __device__ __forceinline__ float gelu_f16_table(float v) {
     return __half2float(__float2half_rn(__fmul_rn(__fmul_rn(0.5f, t), __fadd_rn(1.0f, th))));
 }
 
-static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best) {
+static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best, int pos_value = -1,
+                                     const int* page_table_override = nullptr) {
     if (a.bias) { v0 = __fadd_rn(v0, a.bias[r0]); v1 = __fadd_rn(v1, a.bias[r0 + 1]); }
     switch (a.epi) {
     case EPI_STORE: a.y[r0] = v0; a.y[r0 + 1] = v1; break;
@@ -386,7 +396,7 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
         if (!is_q && !is_k) {
             if (a.rope_neox && e < a.n_rot) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
         } else if (e < a.n_rot) {
-            const float2 cs = a.rope_cs[(size_t)(*a.kv.pos) * (a.n_rot >> 1) + (e >> 1)];
+            const float2 cs = a.rope_cs[(size_t)(pos_value >= 0 ? pos_value : *a.kv.pos) * (a.n_rot >> 1) + (e >> 1)];
             o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
             o1 = __fadd_rn(__fmul_rn(v0, cs.y), __fmul_rn(v1, cs.x));
             if (a.rope_neox) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
@@ -395,8 +405,8 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
             a.y[hb + i0] = __fmul_rn(o0, a.q_scale);
             a.y[hb + i1] = __fmul_rn(o1, a.q_scale);
         } else {
-            const int pos = *a.kv.pos;
-            const int page = a.kv.page_table[pos / a.kv.page_tokens];
+            const int pos = pos_value >= 0 ? pos_value : *a.kv.pos;
+            const int page = (page_table_override ? page_table_override : a.kv.page_table)[pos / a.kv.page_tokens];
             const size_t base = ((size_t)page * a.kv.page_tokens + pos % a.kv.page_tokens) * a.kv.kv_dim;
             __half* dst = (is_k ? a.kv.k_base : a.kv.v_base) + base + hb;
             dst[i0] = __float2half_rn(o0);

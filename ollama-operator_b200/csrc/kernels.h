@@ -74,7 +74,7 @@ struct AttnArgs {
 int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster = 0);
 
 // ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
-constexpr int MEGA_NCW = 16;      // consumer warps per CTA
+constexpr int MEGA_NCW = 15;      // consumer warps per CTA
 struct MegaStage {                // one stage of the layer pipeline, resident in device memory
     int kind = 0;                 // 0 = GEMV, 1 = attention
     GemvArgs g;
@@ -90,9 +90,14 @@ struct MegaLaunch {
     const MegaStage* stages = nullptr;   // device array
     int s_begin = 0, s_end = 0;
     unsigned* grid_count = nullptr;      // zeroed before every launch
+    unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
+    const int* pos = nullptr;            // device scalar: position of the token being decoded
+    const int* page_table = nullptr;     // this slot's page table
+    int n_pages = 0;
     int type = 0, grp = 1, head_dim = 0, cluster = 4, grid = 0;
     uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
     int ns = 0, att_max_local = 0;
+    int inflight = 0;                    // cap on outstanding bulk copies per CTA (0 = the whole ring)
     size_t smem_bytes = 0;
 };
 bool mega_supported(int type, int grp, int head_dim);

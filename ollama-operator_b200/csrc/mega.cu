@@ -30,13 +30,20 @@ using namespace gemvdev;
 using namespace attndev;
 
 constexpr int MEGA_NS_MAX = 8;
+constexpr int MEGA_MAX_PAGES = 256;
 
 struct MegaSmem {            // dynamic shared-memory carve-up (byte offsets), computed on the host
     uint32_t off_red, off_xq, off_xd, off_xs, off_att, off_ring;
     uint32_t stage_bytes;
     int ns;
+    int inflight;            // bulk copies (stages) allowed to be in flight at once, <= ns
 };
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -49,19 +56,17 @@ __device__ __forceinline__ void grid_barrier(unsigned* count, unsigned& epoch, i
     named_bar_sync(1, ntc);                    // every consumer of this CTA has issued its global writes
     if (tid == 0) {
         epoch++;
-        __threadfence();
-        atomicAdd(count, 1u);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(count) : "memory");
         const unsigned target = epoch * gridDim.x;
         while (ld_acquire_gpu(count) < target) {
         }
-        __threadfence();
     }
     named_bar_sync(1, ntc);
 }
 
 template <int TYPE, int NB, int NCW, int GRP, int HD>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
-                                                                   const MegaSmem sm) {
+                                                                   const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MEGA_NS_MAX;
@@ -78,6 +83,11 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     constexpr int ntc = NCW * 32;
     constexpr int NP = TYPE == T_Q4_0 || TYPE == T_Q8_0 ? 2 : TYPE == T_Q4_K ? 3 : 4;
     const int cluster_size = (int)cluster_nctarank();
+    // position and page table of this step: fetched once, used by every layer's KV append and attention
+    __shared__ int s_pos;
+    __shared__ int s_pt[MEGA_MAX_PAGES];
+    for (int i = tid; i < n_pages; i += blockDim.x) s_pt[i] = page_table[i];
+    if (tid == 0) s_pos = *pos_ptr;
 
     if (tid == 0) {
         for (int s = 0; s < sm.ns; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCW); }
@@ -101,6 +111,13 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 for (int64_t row0 = r_begin; row0 < r_end; row0 += S.RT, it++) {
                     const uint32_t s = it % sm.ns;
                     if (it >= (uint32_t)sm.ns) mbar_wait(&empty[s], ((it / sm.ns) - 1) & 1);
+                    // Bound the bytes in flight: a full ring of outstanding copies (19 MB chip-wide) adds
+                    // microseconds of queueing delay to every other memory access of the step (activation
+                    // reads, barrier atomics, KV rows); the ring's capacity is for riding out stalls.
+                    if (it >= (uint32_t)sm.inflight) {
+                        const uint32_t j = it - sm.inflight;
+                        mbar_wait(&full[j % sm.ns], (j / sm.ns) & 1);
+                    }
                     const int rows_here = (int)min((int64_t)S.RT, r_end - row0);
                     uint32_t total = 0;
 #pragma unroll
@@ -119,13 +136,20 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     }
 
     // ===== consumers =====
+    const int pos_now = s_pos;        // written before the __syncthreads above
     uint32_t it = 0, xphase = 0;
     unsigned epoch = 0;
+    double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
+    constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
     for (int st = s_begin; st < s_end; st++) {
         const MegaStage& S = stages[st];
-        if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
+        // optional per-stage timestamps (ns): [0] stage entered, [1] barrier passed, [2] prologue done, [3] stage done
+        unsigned long long* tr = trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 12 : nullptr;
+        if (tr) tr[0] = global_ns();
 
         if (S.kind != 0) {
+            if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);
+            if (tr) tr[1] = global_ns();
             // ---- attention: clusters take KV heads round-robin ----
             const AttnArgs& a = S.at;
             AttnCfg ac;
@@ -133,21 +157,97 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             ac.max_local = S.att_max_local;
             const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
             for (int kvh = my_cluster; kvh < a.n_head_kv; kvh += n_clusters)
-                attn_kv_head<GRP, HD, ntc>(a, ac, kvh, att_smem, tid, xbar, xphase, 1);
+                attn_kv_head<GRP, HD, ntc>(a, ac, kvh, att_smem, tid, xbar, xphase, 1, pos_now, s_pt, tr ? tr + 4 : nullptr);
+            if (tr) tr[2] = tr[3] = global_ns();
             continue;
         }
 
         // ---- GEMV stage ----
         const GemvArgs& a = S.g;
-        const int Sw = S.S, P = S.P, G = S.G, RPG = S.RPG, RT = S.RT, nunits = S.nunits, nbeff = S.nbeff, WPG = Sw * P;
-        {
+        const int Sw = S.S, NW = S.G, RT = S.RT, nunits = S.nunits, nbeff = S.nbeff;
+        const int K = (int)a.W.k, nchunks = K >> 2;
+        const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 127) == 0;
+        // the norm gain does not depend on the previous stage: fetch it while waiting at the barrier
+        float4 gv[MAXC];
+        if (fast && a.pro == PRO_RMSNORM) {
+#pragma unroll
+            for (int c = 0; c < MAXC; c++) {
+                const int i = tid + c * ntc;
+                gv[c] = i < nchunks ? *reinterpret_cast<const float4*>(a.gain + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
+        if (tr) { tr[1] = global_ns(); tr[10] = (unsigned long long)clock64(); }
+
+        if (fast) {
+            // x once into registers (one L2 round trip), RMS statistics, Q8_0 quantisation -- the same
+            // arithmetic as gemvdev::prologue_stats / prologue_q8_0
+            float4 xv[MAXC];
+#pragma unroll
+            for (int c = 0; c < MAXC; c++) {
+                const int i = tid + c * ntc;
+                xv[c] = i < nchunks ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            if (tr) tr[4] = (unsigned long long)clock64();          // (x loads issued)
+            float scale = 1.f;
+            if (a.pro == PRO_RMSNORM) {
+                double ss = 0;
+#pragma unroll
+                for (int c = 0; c < MAXC; c++) {
+                    ss += (double)__fmul_rn(xv[c].x, xv[c].x); ss += (double)__fmul_rn(xv[c].y, xv[c].y);
+                    ss += (double)__fmul_rn(xv[c].z, xv[c].z); ss += (double)__fmul_rn(xv[c].w, xv[c].w);
+                }
+                if (tr) tr[5] = (unsigned long long)clock64();      // (x arrived, squares summed per thread)
+                ss = consumers_sum(ss, dscratch, tid, ntc);
+                const float mean = (float)(ss / (double)K);
+                scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, a.eps)));
+            }
+            if (tr) tr[6] = (unsigned long long)clock64();          // (statistics reduced)
+            const int nbk = K >> 5;
+            // K is a multiple of 128, so a warp's 32 chunks are all inside or all outside the vector:
+            // full-mask shuffles (xor 1,2,4 stay inside the 8 lanes that own one 32-element block)
+            const unsigned gmask = 0xffffffffu;
+#pragma unroll
+            for (int c = 0; c < MAXC; c++) {
+                const int i = tid + c * ntc;
+                if (i < nchunks) {
+                    float4 v = xv[c];
+                    if (a.pro == PRO_RMSNORM) {
+                        v.x = __fmul_rn(__fmul_rn(v.x, scale), gv[c].x); v.y = __fmul_rn(__fmul_rn(v.y, scale), gv[c].y);
+                        v.z = __fmul_rn(__fmul_rn(v.z, scale), gv[c].z); v.w = __fmul_rn(__fmul_rn(v.w, scale), gv[c].w);
+                    }
+                    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+                    amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 1));
+                    amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 2));
+                    amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
+                    const float d = __fdiv_rn(amax, 127.0f);
+                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                    const int q0 = (int)roundf(__fmul_rn(v.x, id)), q1 = (int)roundf(__fmul_rn(v.y, id));
+                    const int q2 = (int)roundf(__fmul_rn(v.z, id)), q3 = (int)roundf(__fmul_rn(v.w, id));
+                    int sum = q0 + q1 + q2 + q3;
+                    sum += __shfl_xor_sync(gmask, sum, 1);
+                    sum += __shfl_xor_sync(gmask, sum, 2);
+                    sum += __shfl_xor_sync(gmask, sum, 4);
+                    const int bq = i >> 3, o = (i & 7) * 4;
+                    uint8_t* dst = xq + (o < 16 ? 0 : nbk * 16) + bq * 16 + (o & 15);
+                    *reinterpret_cast<uint32_t*>(dst) = pack4(q0, q1, q2, q3);
+                    if (o == 0) {
+                        xd[bq] = __half2float(__float2half_rn(d));
+                        xs[bq] = 8 * sum;
+                    }
+                }
+            }
+        } else {
             const ProStats ps = prologue_stats(a, dscratch, tid, ntc);
             if (TYPE == T_Q4_0 || TYPE == T_Q8_0) prologue_q8_0(a, ps, xq, xd, xs, tid, ntc);
             else prologue_q8_K(a, ps, xq, xd, xs, tid, ntc);
-            named_bar_sync(1, ntc);
         }
-        const bool working = warp < G * WPG;
-        const int g = warp / WPG, ch = (warp % WPG) % Sw, rsel = (warp % WPG) / Sw;
+        if (tr) tr[7] = (unsigned long long)clock64();              // (quantised)
+        named_bar_sync(1, ntc);
+        if (tr) tr[8] = (unsigned long long)clock64();              // (block barrier)
+
+        const int worker = warp / Sw, ch = warp % Sw;
+        const bool working = worker < NW;
         XRegs<TYPE> xr[NB];
         int unit[NB];
 #pragma unroll
@@ -157,46 +257,58 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             unit[j] = u < nunits ? u : nunits - 1;
             xr[j].load(xq, xd, xs, unit[j], nunits, valid);
         }
-        named_bar_sync(1, ntc);        // x is in registers: the next stage's prologue may overwrite xq/xd/xs
+        if (tr) { tr[2] = global_ns(); tr[9] = (unsigned long long)clock64(); }
 
         const int64_t pairs = a.W.rows >> 1;
         const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
-        unsigned long long best = 0ull;
         for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
             const uint32_t s = it % sm.ns;
             mbar_wait(&full[s], (it / sm.ns) & 1);
             const int rows_here = (int)min((int64_t)RT, r_end - row0);
             const uint8_t* sp = ring + (size_t)s * sm.stage_bytes;
-            double* redt = red + (size_t)(it & 1) * RT * Sw;
             if (working) {
-                for (int rr = rsel; rr < RPG; rr += P) {
-                    const int r = g * RPG + rr;
-                    if (r >= rows_here) break;
-                    RowPtrs rp;
+                // two rows at a time: twice the independent dp4a chains, and one transposed f64 butterfly
+                // (lanes 0-15 end up with row r, lanes 16-31 with row r+1) instead of two
+                for (int r = 2 * worker; r < rows_here; r += 2 * NW) {
+                    RowPtrs rp0, rp1;
                     const uint8_t* pb = sp;
 #pragma unroll
-                    for (int p = 0; p < NP; p++) { rp.p[p] = pb + (size_t)r * a.W.stride[p]; pb += (size_t)RT * a.W.stride[p]; }
-                    double acc = 0.0;
+                    for (int p = 0; p < NP; p++) {
+                        rp0.p[p] = pb + (size_t)r * a.W.stride[p];
+                        rp1.p[p] = rp0.p[p] + a.W.stride[p];
+                        pb += (size_t)RT * a.W.stride[p];
+                    }
+                    double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
-                    for (int j = 0; j < NB; j++) acc += (double)unit_dot(xr[j], rp, unit[j], nunits);
-                    acc = warp_sum_d(acc);
-                    if (lane == 0) redt[r * Sw + ch] = acc;
+                    for (int j = 0; j < NB; j++) {
+                        acc0 += (double)unit_dot(xr[j], rp0, unit[j], nunits);
+                        acc1 += (double)unit_dot(xr[j], rp1, unit[j], nunits);
+                    }
+                    const bool upper = (lane & 16) != 0;
+                    double keep = upper ? acc1 : acc0;
+                    const double give = upper ? acc0 : acc1;
+                    keep += __shfl_xor_sync(0xffffffffu, give, 16);
+#pragma unroll
+                    for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
+                    if ((lane & 15) == 0) ysum[(size_t)(row0 - r_begin + r + (upper ? 1 : 0)) * Sw + ch] = keep;
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
-            if (working) {
-                if (WPG > 1) named_bar_sync(2 + g, WPG * 32); else __syncwarp();
-                if (ch == 0 && rsel == 0) {
-                    const int r = g * RPG + 2 * lane;
-                    if (2 * lane < RPG && r < rows_here) {
-                        double d0 = 0.0, d1 = 0.0;
-                        for (int k = 0; k < Sw; k++) { d0 += redt[r * Sw + k]; d1 += redt[(r + 1) * Sw + k]; }
-                        epilogue_pair(a, a.epi_row0 + row0 + r, (float)d0, (float)d1, best);
-                    }
-                }
+            if (lane == 0) mbar_arrive(&empty[s]);       // this warp no longer reads stage s
+        }
+        // ---- deferred epilogue: all row sums of this CTA are in shared memory; one thread per row pair,
+        //      so the long-latency parts (f64 exp of SiLU, RoPE table, KV page lookup) are paid once ----
+        named_bar_sync(1, ntc);
+        {
+            unsigned long long best = 0ull;
+            const int npairs = (int)((r_end - r_begin) >> 1);
+            for (int p = tid; p < npairs; p += ntc) {
+                double d0 = 0.0, d1 = 0.0;
+                for (int k = 0; k < Sw; k++) { d0 += ysum[(size_t)(2 * p) * Sw + k]; d1 += ysum[(size_t)(2 * p + 1) * Sw + k]; }
+                epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt);
             }
         }
+        if (tr) tr[3] = global_ns();
     }
 }
 
@@ -210,20 +322,24 @@ int mega_plan_stage(MegaStage& st, int ncw) {
     const bool kq = W.type == T_Q4_K || W.type == T_Q6_K;
     const int nb_max = kq ? 1 : 4;
     st.nunits = (int)(kq ? W.k / 128 : W.k / 32);
-    st.P = 2;
-    // units per lane: the choice that leaves the fewest consumer warps idle, then the fewest idle lanes
+    // S warps cover a row (nbeff units per lane); G = ncw / S "row workers" take the rows of a tile
+    // round-robin.  Pick the units-per-lane that leaves the fewest warps, then lanes, idle.
     int best_idle = 1 << 30;
     for (int nbe = nb_max; nbe >= 1; nbe--) {
         const int S = (st.nunits + 32 * nbe - 1) / (32 * nbe);
-        const int wpg = S * st.P;
-        if (wpg > ncw || ncw / wpg > 13) continue;
-        const int G = ncw / wpg;
-        const int idle = (ncw - G * wpg) * 1024 + (S * 32 * nbe - st.nunits);
+        if (S > ncw) continue;
+        const int G = ncw / S;
+        const int idle = (ncw - G * S) * 1024 + (S * 32 * nbe - st.nunits);
         if (idle < best_idle) { best_idle = idle; st.nbeff = nbe; st.S = S; st.G = G; }
     }
     if (best_idle == (1 << 30)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: k=%lld does not map onto %d consumer warps", (long long)W.k, ncw);
-    st.RPG = 2;
-    st.RT = st.G * st.RPG;
+    // tile = a whole number of worker rounds, close to 36 KB
+    size_t rb = 0;
+    for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
+    int rounds = (int)((40 * 1024) / (rb * st.G * 2));
+    if (rounds < 1) rounds = 1;
+    st.RT = rounds * st.G * 2;           // every worker takes two rows per round
+    st.P = 1; st.RPG = 0;
     return B2_OK;
 }
 
@@ -238,7 +354,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     }
     MegaSmem sm;
     sm.off_red = L.off_red; sm.off_xq = L.off_xq; sm.off_xd = L.off_xd; sm.off_xs = L.off_xs; sm.off_att = L.off_att; sm.off_ring = L.off_ring;
-    sm.stage_bytes = L.stage_bytes; sm.ns = L.ns;
+    sm.stage_bytes = L.stage_bytes; sm.ns = L.ns; sm.inflight = L.inflight > 0 && L.inflight < L.ns ? L.inflight : L.ns;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(L.grid);
     cfg.blockDim = dim3((NCW + 1) * 32);
@@ -251,7 +367,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     at[1].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages));
     return B2_OK;
 }
 
@@ -299,7 +415,7 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     off = (off + 127) / 128 * 128;
     L.off_ring = (uint32_t)off;
     L.stage_bytes = (uint32_t)((tile_bytes_max + 127) / 128 * 128);
-    const size_t cap = 227 * 1024;
+    const size_t cap = 225 * 1024;          // 227 KB per CTA minus the kernel's static shared memory (page table copy)
     if (off + 2 * (size_t)L.stage_bytes > cap) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: shared memory does not fit (%zu B before the ring, %u B per stage)", off, L.stage_bytes);
     L.ns = (int)std::min<size_t>(MEGA_NS_MAX, (cap - off) / L.stage_bytes);
     L.smem_bytes = off + (size_t)L.ns * L.stage_bytes;
@@ -310,6 +426,7 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     }
     if (max_clusters <= 0) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: the kernel does not fit on this device");
     L.grid = max_clusters * L.cluster;
+    if (L.grid < 64) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: only %d co-resident CTAs; the row-sum buffer is sized for >= 64", L.grid);
     return B2_OK;
 }
 

@@ -22,7 +22,7 @@ LOAD_NO_PDL, LOAD_NO_GRAPH, LOAD_NO_MEGA = 1, 2, 4
 SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
     "b2_seq_new", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
-    "b2_get_stats", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
+    "b2_get_stats", "b2_mega_trace", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
 ]
 
 
@@ -75,6 +75,7 @@ def lib() -> C.CDLL:
         L.b2_decode.argtypes = [vp, C.c_int, vp, vp, vp, vp]
         L.b2_decode_greedy.argtypes = [vp, C.c_int, C.c_int32, C.c_int, vp]
         L.b2_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.b2_mega_trace.argtypes = [vp, C.c_int, C.c_int32, vp, C.c_int, ip, ip]
         L.b2_profile_step.argtypes = [vp, C.c_int, C.c_int32, vp, vp]
         L.b2_dequantize.argtypes = [C.c_int, vp, C.c_size_t, vp]
         L.b2_dequantize_repacked.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp]
@@ -257,6 +258,15 @@ class Model:
         out = np.empty(n, dtype=np.float32)
         _check(lib().b2_debug_read(self._h, seq, self.DEBUG_BUFFERS[what], _ptr(out), n))
         return out
+
+    def mega_trace(self, seq: int, tok: int) -> np.ndarray:
+        """Per-CTA, per-stage time stamps (ns) of one step of the persistent kernel: [cta][stage][12]
+        (0-3 stage entered / barrier passed / prologue done / stage done; 4-11 attention phases)."""
+        cap = 160 * (self.info.n_layer * 6) * 12
+        out = np.zeros(cap, dtype=np.uint64)
+        nc, ns = C.c_int(0), C.c_int(0)
+        _check(lib().b2_mega_trace(self._h, seq, tok, _ptr(out), cap, C.byref(nc), C.byref(ns)))
+        return out[: nc.value * ns.value * 12].reshape(nc.value, ns.value, 12)
 
     def stats(self) -> Stats:
         s = Stats()

@@ -1,0 +1,38 @@
+"""Per-stage timing of the persistent decode kernel on llama2-7B (tuning aid)."""
+import importlib, os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+p = importlib.import_module("ollama-operator_b200")
+model = sys.argv[1] if len(sys.argv) > 1 else "llama2-7b"
+ctx = int(sys.argv[2]) if len(sys.argv) > 2 else 512
+path = p.synth.cached_model(model, source="blocks")
+eng = p.engine.Engine(0)
+m = eng.load(path, max_batch=1, max_ctx=ctx + 64)
+seq = m.seq_new()
+m.prefill(seq, p.synth.prompt_tokens(ctx, m.info.n_vocab), want_logits=False)
+m.decode_greedy(seq, 8)
+tr = m.mega_trace(seq, 5).astype(np.int64)
+ncta, nst, _ = tr.shape
+att = tr[:, 15 * 5 + 1, 4:12]
+act = att[:, 0] > 0
+print('attention phases (us, mean over active CTAs): ' + ' '.join(f'{x:.2f}' for x in (np.diff(att[act], axis=1).mean(0) / 1.9e3)), ' total', ((att[act][:, 7] - att[act][:, 0]).mean() / 1.9e3).round(2), 'active ctas', int(act.sum()))
+t0 = tr[:, 0, 0].min()
+names = ["qkv", "attn", "wo", "up", "down"]
+print("ctas", ncta, "stages", nst, "total us", (tr[:, :, 3].max() - t0) / 1e3)
+for L in (0, 1, 15, 31):
+    for k in range(5):
+        s = L * 5 + k
+        ent, bar, pro, done = tr[:, s, 0], tr[:, s, 1], tr[:, s, 2], tr[:, s, 3]
+        print(f"L{L:2d} {names[k]:5s} enter {((ent.min() - t0) / 1e3):8.2f}  barrier wait min {((bar - ent).min() / 1e3):5.2f} mean {((bar - ent).mean() / 1e3):6.2f} max {((bar - ent).max() / 1e3):6.2f}"
+              f"  prologue {((pro - bar).mean() / 1e3):6.2f}  body mean {((done - pro).mean() / 1e3):6.2f} max {((done - pro).max() / 1e3):6.2f}"
+              f"  stage span {((done.max() - ent.min()) / 1e3):6.2f}")
+per = np.zeros(5)
+for s in range(nst):
+    per[s % 5] += (tr[:, s, 3].max() - tr[:, s, 0].min()) / 1e3
+print("sum of stage spans per kind (us):", dict(zip(names, per.round(1))), "sum", per.sum().round(1))
+
+for k, nm in ((0, "qkv"), (3, "up"), (4, "down")):
+    g = tr[:, 15 * 5 + k, :]
+    pts = np.stack([g[:, 10], g[:, 4], g[:, 5], g[:, 6], g[:, 7], g[:, 8], g[:, 9]], 1)
+    pts = np.where(pts == 0, np.nan, pts)
+    print(f"prologue {nm}: barrier->loads issued, ->x arrived+squares, ->stats, ->quantised, ->bar, ->xregs (us):", np.round(np.nanmean(np.diff(pts, axis=1), 0) / 1.9e3, 2), '(SM cycles / 1.9 GHz)')
