@@ -1,17 +1,19 @@
 // attn.cu -- decode attention for one new token over the paged f16 KV cache.
 //
 // Numerics follow llama.cpp's non-flash CPU path step by step (restated in the oracle's
-// `attend`): K and V are f16; the query is rounded to f16 before the dot; scores and the
-// soft-max are f32 with ONE global max and ONE global sum; the normalised probabilities are
-// rounded to f16 before the V product; accumulation is f32.  Staying this close matters: the
-// next op quantises the attention output to Q8_0, and a 1e-4 relative difference here already
-// flips enough int8 roundings to move the logits by 1e-1 (measured; an online-soft-max variant
-// that kept f32 probabilities failed the 2e-2 logit tolerance).
+// `attend`, canonical mode): K and V are f16; the query is rounded to f16; both dot products
+// (q.K over the head dimension, P.V over the cached positions) are evaluated in the lane order of
+// ggml_vec_dot_f16 on an 8-wide SIMD host -- 32 f32 FMA chains and a fixed reduction tree -- which
+// a 32-lane warp reproduces bit for bit; scores and soft-max are f32 with ONE global max and ONE
+// global sum (f64), exp rounded from f64; the normalised probabilities are rounded to f16 before
+// the V product.  Staying this close matters: the next op quantises the attention output to
+// Q8_0, and a 1e-4 relative difference here already flips enough int8 roundings to move the
+// logits by 1e-1 (measured with an online-soft-max variant that kept f32 probabilities).
 //
 // Parallelisation (B200: 148 SMs, thread-block clusters with distributed shared memory):
-// one CLUSTER per (sequence slot, KV head); the cluster's CTAs split the context and serve all
-// query heads that share the KV head (GQA).  The global max and sum are formed by all-gathers
-// of the per-CTA values through DSMEM, the partial outputs are summed in rank 0 -- no global
+// one CLUSTER per (sequence slot, KV head), serving all query heads that share the KV head
+// (GQA).  Scores: positions split over the cluster's CTAs, one warp per position, all-gathered
+// through DSMEM (one exchange).  Output: head dimension split over the CTAs, no merge.  No global
 // scratch, no second kernel.  HBM traffic is K and V once: (pos+1) * kv_dim * 2 * 2 bytes.
 #include <math.h>
 
@@ -80,8 +82,9 @@ int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster
         while (cluster < MAX_CLUSTER && cluster * a.n_head_kv * 2 <= 160) cluster *= 2;
     }
     if (cluster > MAX_CLUSTER) cluster = MAX_CLUSTER;
+    while (cluster > 1 && a.head_dim % (4 * cluster)) cluster /= 2;      // the output dims are split four per warp over the CTAs
     c.cluster = cluster;
-    c.max_local = ((max_ctx + cluster - 1) / cluster + 3) / 4 * 4;
+    c.max_local = (max_ctx + 3) / 4 * 4;
     const size_t smem = attn_smem_bytes(grp, a.head_dim, c.max_local, cluster, ATT_THREADS);
     if (smem > 200 * 1024) B2_FAIL(B2_ERR_UNSUPPORTED, "attn: context %d needs %zu B of shared memory", max_ctx, smem);
 #define B2_ATT_CASE(G, H) if (grp == G && a.head_dim == H) return launch_grp<G, H>(a, c, smem, st, pdl)

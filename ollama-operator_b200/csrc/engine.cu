@@ -501,7 +501,9 @@ int Model::setup_mega(Slot& s) {
     B2_CUDA(cudaMemcpy(s.d_stages, st.data(), st.size() * sizeof(MegaStage), cudaMemcpyHostToDevice));
     L.stages = s.d_stages; L.s_begin = 0; L.s_end = (int)st.size(); L.grid_count = s.d_grid_count;
     L.pos = s.d_pos; L.page_table = s.d_page_table; L.n_pages = pages_per_seq;
-    if (const char* v = getenv("B2_MEGA_INFLIGHT")) L.inflight = atoi(v);
+    L.pf_bytes = 256u << 10;                        // x 132 CTAs = 34 MB of the 126 MB L2
+    if (const char* v = getenv("B2_MEGA_PF_KB")) L.pf_bytes = (uint32_t)atoi(v) << 10;
+    if (const char* v = getenv("B2_MEGA_DEBUG")) L.debug = atoi(v);
     if (pages_per_seq > 256) return B2_OK;          // the kernel keeps the page table in shared memory
     s.mega_ok = true;
     return B2_OK;

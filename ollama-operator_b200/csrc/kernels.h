@@ -97,7 +97,8 @@ struct MegaLaunch {
     int type = 0, grp = 1, head_dim = 0, cluster = 4, grid = 0;
     uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
     int ns = 0, att_max_local = 0;
-    int inflight = 0;                    // cap on outstanding bulk copies per CTA (0 = the whole ring)
+    uint32_t pf_bytes = 0;               // L2 prefetch run-ahead per CTA, bytes (0 = off)
+    int debug = 0;                       // tuning experiments (see mega.cu), results are wrong when set
     size_t smem_bytes = 0;
 };
 bool mega_supported(int type, int grp, int head_dim);

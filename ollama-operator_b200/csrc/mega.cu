@@ -36,7 +36,8 @@ struct MegaSmem {            // dynamic shared-memory carve-up (byte offsets), c
     uint32_t off_red, off_xq, off_xd, off_xs, off_att, off_ring;
     uint32_t stage_bytes;
     int ns;
-    int inflight;            // bulk copies (stages) allowed to be in flight at once, <= ns
+    uint32_t pf_bytes;       // how far (bytes per CTA) the L2 prefetch cursor runs ahead of the ring
+    int debug;               // tuning experiments: 1 = consumers skip the arithmetic, 2 = consumers do not wait for data
 };
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -99,37 +100,62 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 
     if (warp == NCW) {
         // ===== producer: this CTA's tiles of every GEMV stage, in stage order =====
-        if (lane == 0) {
+        if (lane == 0 && !(sm.debug & 2)) {
             const uint64_t pol = l2_policy_evict_first();
-            uint32_t it = 0;
-            for (int st = s_begin; st < s_end; st++) {
-                const MegaStage& S = stages[st];
-                if (S.kind != 0) continue;
-                const QMat& W = S.g.W;
-                const int64_t pairs = W.rows >> 1;
-                const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
-                for (int64_t row0 = r_begin; row0 < r_end; row0 += S.RT, it++) {
-                    const uint32_t s = it % sm.ns;
-                    if (it >= (uint32_t)sm.ns) mbar_wait(&empty[s], ((it / sm.ns) - 1) & 1);
-                    // Bound the bytes in flight: a full ring of outstanding copies (19 MB chip-wide) adds
-                    // microseconds of queueing delay to every other memory access of the step (activation
-                    // reads, barrier atomics, KV rows); the ring's capacity is for riding out stalls.
-                    if (it >= (uint32_t)sm.inflight) {
-                        const uint32_t j = it - sm.inflight;
-                        mbar_wait(&full[j % sm.ns], (j / sm.ns) & 1);
-                    }
-                    const int rows_here = (int)min((int64_t)S.RT, r_end - row0);
-                    uint32_t total = 0;
-#pragma unroll
-                    for (int p = 0; p < NP; p++) total += (uint32_t)rows_here * W.stride[p];
-                    mbar_expect_tx(&full[s], total);
-                    uint8_t* dst = ring + (size_t)s * sm.stage_bytes;
-#pragma unroll
-                    for (int p = 0; p < NP; p++) {
-                        bulk_g2s(dst, W.plane[p] + (size_t)row0 * W.stride[p], (uint32_t)rows_here * W.stride[p], &full[s], pol);
-                        dst += (size_t)S.RT * W.stride[p];
-                    }
+            // cursor over (stage, tile) pairs; two of them walk the same sequence: `f` feeds the
+            // shared-memory ring, `p` runs up to sm.pf_bytes further ahead issuing L2 prefetches, so
+            // that HBM keeps streaming while the consumers sit in a barrier, a prologue or the
+            // attention (the ring alone covers ~3 us of HBM time, L2 holds tens of MB more)
+            struct Cursor {
+                int st; int64_t row0, r_end; int RT;
+            };
+            auto seek = [&](Cursor& c) {         // position on the first tile of the next GEMV stage at or after c.st
+                for (; c.st < s_end; c.st++) {
+                    const MegaStage& S = stages[c.st];
+                    if (S.kind != 0) continue;
+                    const int64_t pairs = S.g.W.rows >> 1;
+                    c.row0 = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x);
+                    c.r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
+                    c.RT = S.RT;
+                    if (c.row0 < c.r_end) return;
                 }
+            };
+            auto advance = [&](Cursor& c) {
+                c.row0 += c.RT;
+                if (c.row0 >= c.r_end) { c.st++; seek(c); }
+            };
+            Cursor f{s_begin, 0, 0, 0}, p{s_begin, 0, 0, 0};
+            seek(f); seek(p);
+            long long ahead = 0;                  // bytes prefetched to L2 but not yet requested for the ring
+            uint32_t it = 0;
+            while (f.st < s_end) {
+                while (p.st < s_end && ahead < (long long)sm.pf_bytes) {
+                    const QMat& W = stages[p.st].g.W;
+                    const int rows_here = (int)min((int64_t)p.RT, p.r_end - p.row0);
+#pragma unroll
+                    for (int pl = 0; pl < NP; pl++) {
+                        prefetch_l2(W.plane[pl] + (size_t)p.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl]);
+                        ahead += (long long)rows_here * W.stride[pl];
+                    }
+                    advance(p);
+                }
+                const QMat& W = stages[f.st].g.W;
+                const uint32_t s = it % sm.ns;
+                if (it >= (uint32_t)sm.ns) mbar_wait(&empty[s], ((it / sm.ns) - 1) & 1);
+                const int rows_here = (int)min((int64_t)f.RT, f.r_end - f.row0);
+                uint32_t total = 0;
+#pragma unroll
+                for (int pl = 0; pl < NP; pl++) total += (uint32_t)rows_here * W.stride[pl];
+                mbar_expect_tx(&full[s], total);
+                uint8_t* dst = ring + (size_t)s * sm.stage_bytes;
+#pragma unroll
+                for (int pl = 0; pl < NP; pl++) {
+                    bulk_g2s(dst, W.plane[pl] + (size_t)f.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl], &full[s], pol);
+                    dst += (size_t)f.RT * W.stride[pl];
+                }
+                ahead -= total;
+                advance(f);
+                it++;
             }
         }
         return;
@@ -258,15 +284,22 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             xr[j].load(xq, xd, xs, unit[j], nunits, valid);
         }
         if (tr) { tr[2] = global_ns(); tr[9] = (unsigned long long)clock64(); }
+        // the attention stage that follows will read K/V rows that already exist: pull them into L2
+        // now, while this stage streams its weights
+        if (st + 1 < s_end && stages[st + 1].kind != 0) {
+            const AttnArgs& na = stages[st + 1].at;
+            const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
+            for (int kvh = my_cluster; kvh < na.n_head_kv; kvh += n_clusters) attn_prefetch<GRP, HD, ntc>(na, cluster_size, kvh, tid, pos_now, s_pt);
+        }
 
         const int64_t pairs = a.W.rows >> 1;
         const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
         for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
             const uint32_t s = it % sm.ns;
-            mbar_wait(&full[s], (it / sm.ns) & 1);
+            if (!(sm.debug & 2)) mbar_wait(&full[s], (it / sm.ns) & 1);
             const int rows_here = (int)min((int64_t)RT, r_end - row0);
             const uint8_t* sp = ring + (size_t)s * sm.stage_bytes;
-            if (working) {
+            if (working && !(sm.debug & 1)) {
                 // two rows at a time: twice the independent dp4a chains, and one transposed f64 butterfly
                 // (lanes 0-15 end up with row r, lanes 16-31 with row r+1) instead of two
                 for (int r = 2 * worker; r < rows_here; r += 2 * NW) {
@@ -294,7 +327,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);       // this warp no longer reads stage s
+            if (lane == 0 && !(sm.debug & 2)) mbar_arrive(&empty[s]);       // this warp no longer reads stage s
         }
         // ---- deferred epilogue: all row sums of this CTA are in shared memory; one thread per row pair,
         //      so the long-latency parts (f64 exp of SiLU, RoPE table, KV page lookup) are paid once ----
@@ -354,7 +387,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     }
     MegaSmem sm;
     sm.off_red = L.off_red; sm.off_xq = L.off_xq; sm.off_xd = L.off_xd; sm.off_xs = L.off_xs; sm.off_att = L.off_att; sm.off_ring = L.off_ring;
-    sm.stage_bytes = L.stage_bytes; sm.ns = L.ns; sm.inflight = L.inflight > 0 && L.inflight < L.ns ? L.inflight : L.ns;
+    sm.stage_bytes = L.stage_bytes; sm.ns = L.ns; sm.pf_bytes = L.pf_bytes; sm.debug = L.debug;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(L.grid);
     cfg.blockDim = dim3((NCW + 1) * 32);
@@ -410,7 +443,8 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     L.off_xd = (uint32_t)off; off += (size_t)(kq ? k_max / 256 : k_max / 32) * 4; off = (off + 15) / 16 * 16;
     L.off_xs = (uint32_t)off; off += (size_t)(kq ? k_max / 16 : k_max / 32) * 4; off = (off + 15) / 16 * 16;
     L.off_att = (uint32_t)off;
-    L.att_max_local = ((max_ctx + L.cluster - 1) / L.cluster + 3) / 4 * 4;
+    L.att_max_local = (max_ctx + 3) / 4 * 4;
+    if (L.head_dim % (4 * L.cluster)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: head_dim %d does not split over a cluster of %d", L.head_dim, L.cluster);
     off += attndev::attn_smem_bytes(L.grp, L.head_dim, L.att_max_local, L.cluster, MEGA_NCW * 32);
     off = (off + 127) / 128 * 128;
     L.off_ring = (uint32_t)off;

@@ -714,6 +714,27 @@ static void add_bias(float *y, const ref_tensor *b, int64_t n) {
     for (int64_t i = 0; i < n; i++) y[i] += bb[i];
 }
 
+/* ggml_vec_dot_f16 as ggml's 8-wide SIMD builds (AVX/AVX2/NEON-f32 style, GGML_F16_STEP = 32)
+ * evaluate it [upstream]: 32 f32 lanes L = i mod 32, each an FMA chain over the elements it owns,
+ * then the fixed reduction  (L,L+16) -> (L,L+8) -> (L,L+4) -> hadd -> hadd ; elements beyond the
+ * last multiple of 32 are added in f64.  `stride*` let the same code walk a K row (stride 1) and
+ * a V column (stride = row length).  The result is what the x86 servers the reference deploys on
+ * compute, and -- unlike an f64 running sum over hundreds of cached positions -- it is cheap to
+ * reproduce bit for bit on a 32-lane GPU warp. */
+static float dot_f16_lanes32(int64_t n, const uint16_t *x, int64_t stride_x, const uint16_t *y, int64_t stride_y, int64_t n_simd) {
+    float lane[32];
+    for (int l = 0; l < 32; l++) lane[l] = 0.0f;
+    for (int64_t i = 0; i < n_simd; i++)
+        lane[i & 31] = fmaf(h2f(x[i * stride_x]), h2f(y[i * stride_y]), lane[i & 31]);
+    for (int l = 0; l < 16; l++) lane[l] += lane[l + 16];
+    for (int l = 0; l < 8; l++) lane[l] += lane[l + 8];
+    for (int l = 0; l < 4; l++) lane[l] += lane[l + 4];
+    const float res = (lane[0] + lane[1]) + (lane[2] + lane[3]);
+    double sumf = (double)res;
+    for (int64_t i = n_simd; i < n; i++) sumf += (double)(h2f(x[i * stride_x]) * h2f(y[i * stride_y]));
+    return (float)sumf;
+}
+
 /* Attention for one new token over cache rows [0,pos]; llama.cpp's non-flash path
  * [upstream]: kq = K(f16).q(->f16), f32 result; soft_max_ext(kq*scale); probabilities
  * ->f16; out = V(f16)^T.p with f64 accumulate of f32 products. */
@@ -727,7 +748,25 @@ static void attend(ref_ctx *c, int il, int pos, float scale) {
         float *sc = c->scores + (size_t)h * m->n_ctx;
         const float *q = c->q + (size_t)h * hd;
         float *o = c->att + (size_t)h * hd;
-        if (c->faithful) {
+        if (c->faithful == 2) {
+            /* canonical: both dots in the 32-lane SIMD order above.  K rows: hd elements (the tail
+             * beyond a multiple of 32, e.g. phi-2's 80, goes through the f64 leftover loop).  V
+             * columns: llama.cpp pads the number of cached positions to a multiple of 32 with
+             * masked (probability 0) entries, so every position sits in a SIMD lane and there is
+             * no leftover loop. */
+            uint16_t q16[512];
+            uint16_t *p16 = (uint16_t *)malloc((size_t)(pos + 1) * 2);
+            for (int d = 0; d < hd; d++) q16[d] = f2h(q[d]);
+            for (int t = 0; t <= pos; t++) {
+                const uint16_t *kr = c->k16[il] + (size_t)t * nkv + (size_t)hk * hd;
+                sc[t] = dot_f16_lanes32(hd, kr, 1, q16, 1, hd & ~31) * scale;
+            }
+            softmax_canon(sc, pos + 1);
+            for (int t = 0; t <= pos; t++) p16[t] = f2h(sc[t]);
+            for (int d = 0; d < hd; d++)
+                o[d] = dot_f16_lanes32(pos + 1, c->v16[il] + (size_t)hk * hd + d, (int64_t)nkv, p16, 1, pos + 1);
+            free(p16);
+        } else if (c->faithful) {
             uint16_t q16[512];
             for (int d = 0; d < hd; d++) q16[d] = f2h(q[d]);
             for (int t = 0; t <= pos; t++) {
@@ -736,7 +775,7 @@ static void attend(ref_ctx *c, int il, int pos, float scale) {
                 for (int d = 0; d < hd; d++) s += (double)(h2f(kr[d]) * h2f(q16[d]));
                 sc[t] = (float)s * scale;
             }
-            if (c->faithful == 2) softmax_canon(sc, pos + 1); else ref_softmax(sc, pos + 1);
+            ref_softmax(sc, pos + 1);
             for (int d = 0; d < hd; d++) {
                 double s = 0;
                 for (int t = 0; t <= pos; t++)
@@ -758,6 +797,25 @@ static void attend(ref_ctx *c, int il, int pos, float scale) {
             }
         }
     }
+}
+
+/* Canonical (mode 2) attention of one token over n cached rows, for the kernel tests:
+ * q [n_head*hd] f32, k / v [n][n_head_kv*hd] f16, out [n_head*hd]. */
+void ref_attention_canon(const float *q, const uint16_t *k, const uint16_t *v, int n, int n_head, int n_head_kv, int hd, float scale, float *out) {
+    const int grp = n_head / n_head_kv;
+    const size_t nkv = (size_t)n_head_kv * hd;
+    float *sc = (float *)malloc((size_t)n * 4);
+    uint16_t *p16 = (uint16_t *)malloc((size_t)n * 2);
+    for (int h = 0; h < n_head; h++) {
+        const int hk = h / grp;
+        uint16_t q16[512];
+        for (int d = 0; d < hd; d++) q16[d] = f2h(q[(size_t)h * hd + d]);
+        for (int t = 0; t < n; t++) sc[t] = dot_f16_lanes32(hd, k + (size_t)t * nkv + (size_t)hk * hd, 1, q16, 1, hd & ~31) * scale;
+        softmax_canon(sc, n);
+        for (int t = 0; t < n; t++) p16[t] = f2h(sc[t]);
+        for (int d = 0; d < hd; d++) out[(size_t)h * hd + d] = dot_f16_lanes32(n, v + (size_t)hk * hd + d, (int64_t)nkv, p16, 1, n);
+    }
+    free(sc); free(p16);
 }
 
 static void store_kv(ref_ctx *c, int il, int pos) {

@@ -65,7 +65,8 @@ float ref_vec_dot_q6_K_q8_K(int64_t n, const void *vx, const void *vy);
  *   1  ggml's generic C path: x quantised to the weight type's vec_dot type, exact integer
  *      block dots, per-block float terms added in f32, block after block;
  *   2  "canonical": the same terms, added in f64 and rounded to f32 once, exp/tanh rounded
- *      from f64 -- order-free, so the CUDA kernels can (and must) match it bit for bit.
+ *      from f64 -- order-free, so the CUDA kernels can (and must) match it bit for bit.  (The
+ *      attention dots of mode 2 follow ggml's 32-lane SIMD f16 dot instead; see ggml_ref.c.)
  * threads<=0 -> all cores. */
 void ref_mul_mat_vec(int wtype, const void *W, int64_t rows, int64_t k,
                      const float *x, float *y, int faithful, int threads);
@@ -77,6 +78,8 @@ void ref_layer_norm(const float *x, const float *g, const float *b, float *y, in
  * n_head vectors of head_dim; rotates the first n_rot dims. */
 void ref_rope(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode);
 void ref_softmax(float *x, int64_t n);
+/* canonical-mode attention of one token (see ggml_ref.c); k, v: [n][n_head_kv*hd] f16 */
+void ref_attention_canon(const float *q, const uint16_t *k, const uint16_t *v, int n, int n_head, int n_head_kv, int hd, float scale, float *out);
 
 /* ---- whole-model forward ------------------------------------------------------- */
 enum { REF_ARCH_LLAMA = 0, REF_ARCH_PHI2 = 1 };

@@ -69,6 +69,7 @@ def lib() -> C.CDLL:
         L.ref_layer_norm.argtypes = [vp, vp, vp, vp, i64, C.c_float]
         L.ref_rope.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]
         L.ref_softmax.argtypes = [vp, i64]
+        L.ref_attention_canon.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]
         L.ref_ctx_new.restype = vp
         L.ref_ctx_new.argtypes = [C.POINTER(Model), C.c_int, C.c_int]
         L.ref_ctx_free.argtypes = [vp]
@@ -130,6 +131,14 @@ def rope(x, n_head, head_dim, n_rot, pos, freq_base, mode):
     x = np.array(x, dtype=np.float32, order="C")
     lib().ref_rope(_p(x), n_head, head_dim, n_rot, pos, freq_base, mode)
     return x
+
+
+def attention_canon(q, k, v, n_head, n_head_kv, hd, scale):
+    """Canonical-mode attention of one token: q f32 [n_head*hd], k / v f16 [n][n_head_kv*hd]."""
+    q = np.ascontiguousarray(q, np.float32); k = np.ascontiguousarray(k, np.float16); v = np.ascontiguousarray(v, np.float16)
+    out = np.empty(n_head * hd, dtype=np.float32)
+    lib().ref_attention_canon(_p(q), _p(k), _p(v), k.shape[0], n_head, n_head_kv, hd, scale, _p(out))
+    return out
 
 
 class OracleModel:

@@ -97,28 +97,10 @@ def test_gemv_edge_inputs(pkg, oracle):
             assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (t, np.abs(got - want).max())
 
 
-def _attn_ref(q, k, v, n_head, n_head_kv, hd, scale):
-    """llama.cpp non-flash path in numpy (same steps as oracle/ggml_ref.c `attend`, canonical
-    mode): f16 q, exact products summed in f64, f32 soft-max with exp rounded from f64, f16
-    probabilities, f64 sum of exact products."""
-    n = k.shape[0]
-    grp = n_head // n_head_kv
-    out = np.zeros(n_head * hd, np.float32)
-    q16 = q.astype(np.float16).astype(np.float64)
-    for h in range(n_head):
-        kh = k[:, (h // grp) * hd:(h // grp + 1) * hd].astype(np.float64)
-        vh = v[:, (h // grp) * hd:(h // grp + 1) * hd].astype(np.float64)
-        s = (kh @ q16[h * hd:(h + 1) * hd]).astype(np.float32) * np.float32(scale)
-        p = np.exp((s - s.max()).astype(np.float64)).astype(np.float32)
-        p = (p * np.float32(1.0 / p.astype(np.float64).sum())).astype(np.float16).astype(np.float64)
-        out[h * hd:(h + 1) * hd] = (p @ vh).astype(np.float32)
-    return out
-
-
 @pytest.mark.parametrize("n_ctx", [1, 2, 63, 64, 65, 300, 1024, 2500])
 @pytest.mark.parametrize("n_head,n_head_kv,hd", [(4, 4, 128), (8, 2, 64), (8, 1, 128), (4, 2, 80)])
 @pytest.mark.parametrize("cluster", [1, 4, 8])
-def test_attention_matches_reference(pkg, n_ctx, n_head, n_head_kv, hd, cluster):
+def test_attention_matches_reference(pkg, oracle, n_ctx, n_head, n_head_kv, hd, cluster):
     if cluster == 8 and n_ctx not in (65, 2500):
         pytest.skip("covered by the other cluster sizes")
     rng = np.random.default_rng(n_ctx * 7 + n_head)
@@ -126,8 +108,9 @@ def test_attention_matches_reference(pkg, n_ctx, n_head, n_head_kv, hd, cluster)
     k = rng.standard_normal((n_ctx, n_head_kv * hd)).astype(np.float16)
     v = rng.standard_normal((n_ctx, n_head_kv * hd)).astype(np.float16)
     scale = hd ** -0.5
-    want = _attn_ref(q, k, v, n_head, n_head_kv, hd, scale)
+    # oracle canonical mode: llama.cpp's non-flash path with both dots in ggml's 32-lane SIMD order
+    want = oracle.attention_canon(q, k, v, n_head, n_head_kv, hd, scale)
     got = pkg.engine.attn_decode(q, k, v, n_head, n_head_kv, hd, scale, cluster)
-    # every step is order-free (f64 sums of exact products), so the kernel must agree bit for bit
-    # for any split of the context over the cluster
+    # a warp reproduces the SIMD lane order exactly, so the kernel must agree bit for bit for any
+    # split of the work over the cluster
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), np.max(np.abs(got - want))

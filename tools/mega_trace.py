@@ -13,9 +13,9 @@ m.prefill(seq, p.synth.prompt_tokens(ctx, m.info.n_vocab), want_logits=False)
 m.decode_greedy(seq, 8)
 tr = m.mega_trace(seq, 5).astype(np.int64)
 ncta, nst, _ = tr.shape
-att = tr[:, 15 * 5 + 1, 4:12]
+att = tr[:, 15 * 5 + 1, 4:10]
 act = att[:, 0] > 0
-print('attention phases (us, mean over active CTAs): ' + ' '.join(f'{x:.2f}' for x in (np.diff(att[act], axis=1).mean(0) / 1.9e3)), ' total', ((att[act][:, 7] - att[act][:, 0]).mean() / 1.9e3).round(2), 'active ctas', int(act.sum()))
+print('attention phases (us, mean over active CTAs): ' + ' '.join(f'{x:.2f}' for x in (np.diff(att[act], axis=1).mean(0) / 1.9e3)), ' total', ((att[act][:, 5] - att[act][:, 0]).mean() / 1.9e3).round(2), 'active ctas', int(act.sum()))
 t0 = tr[:, 0, 0].min()
 names = ["qkv", "attn", "wo", "up", "down"]
 print("ctas", ncta, "stages", nst, "total us", (tr[:, :, 3].max() - t0) / 1e3)
