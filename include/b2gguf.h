@@ -114,9 +114,10 @@ int b2_get_stats(const b2_model* m, b2_stats* out);
  * attention, wo, gate|up, down).  Tuning aid. */
 int b2_mega_trace(b2_model* m, int seq, int32_t tok, uint64_t* out, int cap, int* n_cta, int* n_stage);
 /* One decode step for `seq` (like b2_decode with one sequence) run with a CUDA event after every
- * kernel: class_ms[8] / class_launches[8] receive device milliseconds and launch counts per
+ * kernel: class_ms[9] / class_launches[9] receive device milliseconds and launch counts per
  * kernel class {0 step-begin, 1 qkv gemv, 2 attention, 3 wo gemv, 4 gate/up gemv, 5 down gemv,
- * 6 head gemv, 7 step-end}.  Stands in for llama.cpp's per-op timings (GGML_PERF) [upstream]. */
+ * 6 head gemv, 7 step-end, 8 persistent all-layers kernel (then classes 1-5 stay empty)}.
+ * Stands in for llama.cpp's per-op timings (GGML_PERF) [upstream]. */
 int b2_profile_step(b2_model* m, int seq, int32_t tok, float* class_ms, int* class_launches);
 
 /* ---- test / tooling hooks (host buffers in, host buffers out) ------------------------------ */

@@ -82,7 +82,7 @@ int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster
         while (cluster < MAX_CLUSTER && cluster * a.n_head_kv * 2 <= 160) cluster *= 2;
     }
     if (cluster > MAX_CLUSTER) cluster = MAX_CLUSTER;
-    while (cluster > 1 && a.head_dim % (4 * cluster)) cluster /= 2;      // the output dims are split four per warp over the CTAs
+    while (cluster > 1 && a.head_dim % (8 * cluster)) cluster /= 2;      // the output dims are split eight per warp over the CTAs
     c.cluster = cluster;
     c.max_local = (max_ctx + 3) / 4 * 4;
     const size_t smem = attn_smem_bytes(grp, a.head_dim, c.max_local, cluster, ATT_THREADS);

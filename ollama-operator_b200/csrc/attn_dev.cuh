@@ -77,6 +77,31 @@ static __device__ __forceinline__ void attn_prefetch(const AttnArgs& a, int clus
     }
 }
 
+// Eight independent 32-lane sums at once, each reduced in exactly the order of reduce_lanes32: at
+// the xor-16 / 8 / 4 steps a lane keeps half of its values and hands the other half to its partner,
+// so 9 shuffles do the work of 40.  Lane L ends up with product number ((L>>4)&1)*4 + ((L>>3)&1)*2 +
+// ((L>>2)&1); the four lanes that share bits 2..4 hold the same value.
+__device__ __forceinline__ float reduce8_lanes32(const float (&v)[8], int lane) {
+    const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
+    float k[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const float keep = b4 ? v[4 + i] : v[i], send = b4 ? v[i] : v[4 + i];
+        k[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    float m[2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const float keep = b3 ? k[2 + i] : k[i], send = b3 ? k[i] : k[2 + i];
+        m[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    float r = (b2 ? m[1] : m[0]) + __shfl_xor_sync(0xffffffffu, b2 ? m[0] : m[1], 4);
+    r += __shfl_xor_sync(0xffffffffu, r, 1);
+    r += __shfl_xor_sync(0xffffffffu, r, 2);
+    return r;
+}
+__device__ __forceinline__ int reduce8_index(int lane) { return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1); }
+
 // Attention of one KV head (all GRP query heads that share it) by the NT calling threads of every
 // CTA of the cluster.  `xb` is this CTA's exchange barrier (initialised to `cluster` arrivals,
 // same shared-memory offset in every CTA), `xphase` its running phase; `barid` a CTA-local named
@@ -88,7 +113,9 @@ static __device__ __forceinline__ void attn_prefetch(const AttnArgs& a, int clus
 //   2. soft-max over all positions, redundantly in every CTA (no exchange): one max, exp rounded
 //      from f64, f64 sum, probabilities rounded to f16 as ggml does before the V product.
 //   3. output: the head dimension is split over the cluster's CTAs (no merge needed); lane L owns the
-//      positions t = L mod 32 as an FMA chain -- again ggml's lane structure -- four dims per warp.
+//      positions t = L mod 32 as an FMA chain -- again ggml's lane structure -- eight dims per warp.
+// The whole thing is latency-bound (a few hundred KB per head), so the code is organised around
+// having many independent loads in flight and few dependent shuffles.
 template <int GRP, int HD, int NT>
 static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh, uint8_t* smem_raw, int tid, uint64_t* xb, uint32_t& xphase,
                                                  int barid, int pos_value = -1, const int* page_table_override = nullptr,
@@ -97,6 +124,9 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     stamp(0);
     constexpr int NWARP = NT / 32;
     constexpr int HD32 = HD & ~31;             // dims that go through the SIMD lanes
+    constexpr int NI = HD32 / 32 > 0 ? HD32 / 32 : 1;
+    static_assert(8 % GRP == 0, "GRP must divide 8");
+    constexpr int PB = 8 / GRP;                // positions per reduce8 batch (PB * GRP = 8 dot products)
     const int lane = tid & 31, warp = tid >> 5;
     const uint32_t rk = cluster_ctarank();
     const int CL = c.cluster, maxc = c.max_local;
@@ -112,8 +142,7 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     float* qs = reinterpret_cast<float*>(wsum + ((NWARP * GRP + 1) & ~1));   // [GRP][HD] f16-rounded query
     float* sc = qs + GRP * HD;                                       // [GRP][maxc] scores -> probabilities (all positions)
     float* wred = sc + (size_t)GRP * maxc;                           // [NWARP][GRP]
-    float* ml = wred + NWARP * GRP;                                  // [2][GRP] max, 1/sum
-    int* rowoff = reinterpret_cast<int*>(ml + 2 * GRP);              // [maxc] element offset of every cached row inside a layer's pool
+    int* rowoff = reinterpret_cast<int*>(wred + NWARP * GRP);        // [maxc] element offset of every cached row inside a layer's pool
 
     for (int i = tid; i < GRP * HD; i += NT) qs[i] = __half2float(__float2half_rn(__ldcg(a.q + (size_t)kvh * GRP * HD + i)));
     // page-table walk once per position, in parallel, instead of inside the latency-bound loops below
@@ -124,41 +153,52 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     // ---- 1. scores of this CTA's slice of the context ---------------------------------------------
     const int per = (n + CL - 1) / CL;
     const int t_begin = min(n, (int)rk * per), t_end = min(n, t_begin + per);
-    // U positions per warp are in flight at once (the loads of a batch are issued before any of them
-    // is used): the phase is bound by memory latency, not by arithmetic
-    constexpr int U = GRP >= 4 ? 4 : (HD <= 128 ? 12 : 8);
-    constexpr int NI = HD32 / 32 > 0 ? HD32 / 32 : 1;
-    for (int t0 = t_begin + warp; t0 < t_end; t0 += NWARP * U) {
-        const __half* kr[U];
-        float kv[U][NI];
+    {
+        float qreg[GRP][NI];
 #pragma unroll
-        for (int u = 0; u < U; u++) {
-            const int t = min(t0 + u * NWARP, t_end - 1);
-            kr[u] = k_base + rowoff[t];
+        for (int g = 0; g < GRP; g++)
 #pragma unroll
-            for (int i = 0; i < HD32 / 32; i++) kv[u][i] = __half2float(kr[u][i * 32 + lane]);
-        }
+            for (int i = 0; i < HD32 / 32; i++) qreg[g][i] = qs[g * HD + i * 32 + lane];
+        // a warp takes PB consecutive positions per batch and keeps NBATCH batches of loads in flight
+        constexpr int NBATCH = 2;
+        for (int t0 = t_begin + warp * PB; t0 < t_end; t0 += NWARP * PB * NBATCH) {
+            float kv[NBATCH][PB][NI];
 #pragma unroll
-        for (int u = 0; u < U; u++) {
-            const int t = t0 + u * NWARP;
-            if (t < t_end) {
-                float acc[GRP];
+            for (int bq = 0; bq < NBATCH; bq++)
 #pragma unroll
-                for (int g = 0; g < GRP; g++) {
-                    acc[g] = 0.f;
+                for (int u = 0; u < PB; u++) {
+                    const int t = min(t0 + bq * NWARP * PB + u, t_end - 1);
+                    const __half* kr = k_base + rowoff[t];
 #pragma unroll
-                    for (int i = 0; i < HD32 / 32; i++) acc[g] = fmaf(kv[u][i], qs[g * HD + i * 32 + lane], acc[g]);
-                    acc[g] = reduce_lanes32(acc[g]);
-                    if (HD32 != HD) {                   // ggml adds the tail beyond a multiple of 32 in f64
-                        double sumf = (double)acc[g];
-                        for (int d = HD32; d < HD; d++) sumf += (double)__fmul_rn(__half2float(kr[u][d]), qs[g * HD + d]);
-                        acc[g] = (float)sumf;
-                    }
-                    acc[g] = __fmul_rn(acc[g], scale);
+                    for (int i = 0; i < HD32 / 32; i++) kv[bq][u][i] = __half2float(kr[i * 32 + lane]);
                 }
-                if (lane < CL) {
 #pragma unroll
-                    for (int g = 0; g < GRP; g++) dsmem_st_f32(dsmem_addr(sc + (size_t)g * maxc + t, (uint32_t)lane), acc[g]);
+            for (int bq = 0; bq < NBATCH; bq++) {
+                const int tb = t0 + bq * NWARP * PB;
+                if (tb < t_end) {
+                    float prod[8];
+#pragma unroll
+                    for (int u = 0; u < PB; u++)
+#pragma unroll
+                        for (int g = 0; g < GRP; g++) {
+                            float acc = 0.f;
+#pragma unroll
+                            for (int i = 0; i < HD32 / 32; i++) acc = fmaf(kv[bq][u][i], qreg[g][i], acc);
+                            prod[u * GRP + g] = acc;
+                        }
+                    float r = reduce8_lanes32(prod, lane);
+                    const int idx = reduce8_index(lane), u = idx / GRP, g = idx % GRP, t = tb + u;
+                    if (t < t_end) {
+                        if (HD32 != HD) {               // ggml adds the tail beyond a multiple of 32 in f64
+                            const __half* kr = k_base + rowoff[t];
+                            double sumf = (double)r;
+                            for (int d = HD32; d < HD; d++) sumf += (double)__fmul_rn(__half2float(kr[d]), qs[g * HD + d]);
+                            r = (float)sumf;
+                        }
+                        r = __fmul_rn(r, scale);
+                        // the four lanes that hold this product write it to up to four peers
+                        for (int peer = lane & 3; peer < CL; peer += 4) dsmem_st_f32(dsmem_addr(sc + (size_t)g * maxc + t, (uint32_t)peer), r);
+                    }
                 }
             }
         }
@@ -168,92 +208,97 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     stamp(3);
 
     // ---- 2. soft-max over all positions (ggml soft_max: one max, expf, f64 sum, scale by 1/sum) ------
-    float lmax[GRP];
+    float M[GRP], inv[GRP];
+    {
+        float lmax[GRP];
 #pragma unroll
-    for (int g = 0; g < GRP; g++) lmax[g] = -INFINITY;
-    for (int t = tid; t < n; t += NT) {
+        for (int g = 0; g < GRP; g++) lmax[g] = -INFINITY;
+        for (int t = tid; t < n; t += NT) {
 #pragma unroll
-        for (int g = 0; g < GRP; g++) lmax[g] = fmaxf(lmax[g], sc[(size_t)g * maxc + t]);
-    }
-#pragma unroll
-    for (int g = 0; g < GRP; g++) {
-        const float m = warp_max(lmax[g]);
-        if (lane == 0) wred[warp * GRP + g] = m;
-    }
-    named_bar_sync(barid, NT);
-    if (tid < GRP) {
-        float M = wred[tid];
-        for (int w = 1; w < NWARP; w++) M = fmaxf(M, wred[w * GRP + tid]);
-        ml[tid] = M;
-    }
-    named_bar_sync(barid, NT);
-    double lsum[GRP];
-#pragma unroll
-    for (int g = 0; g < GRP; g++) lsum[g] = 0.0;
-    for (int t = tid; t < n; t += NT) {
+            for (int g = 0; g < GRP; g++) lmax[g] = fmaxf(lmax[g], sc[(size_t)g * maxc + t]);
+        }
 #pragma unroll
         for (int g = 0; g < GRP; g++) {
-            const float e = (float)exp((double)__fsub_rn(sc[(size_t)g * maxc + t], ml[g]));
-            sc[(size_t)g * maxc + t] = e;
-            lsum[g] += (double)e;
+            const float m = warp_max(lmax[g]);
+            if (lane == 0) wred[warp * GRP + g] = m;
         }
-    }
+        named_bar_sync(barid, NT);
 #pragma unroll
-    for (int g = 0; g < GRP; g++) {
-        const double s = warp_sum_d(lsum[g]);
-        if (lane == 0) wsum[warp * GRP + g] = s;
-    }
-    named_bar_sync(barid, NT);
-    if (tid < GRP) {
-        double S = 0;
-        for (int w = 0; w < NWARP; w++) S += wsum[w * GRP + tid];
-        ml[GRP + tid] = (float)(1.0 / S);
-    }
-    named_bar_sync(barid, NT);
-    for (int t = tid; t < n; t += NT) {
+        for (int g = 0; g < GRP; g++) {
+            M[g] = wred[g];
 #pragma unroll
-        for (int g = 0; g < GRP; g++)
-            sc[(size_t)g * maxc + t] = __half2float(__float2half_rn(__fmul_rn(sc[(size_t)g * maxc + t], ml[GRP + g])));
+            for (int w = 1; w < NWARP; w++) M[g] = fmaxf(M[g], wred[w * GRP + g]);
+        }
+        double lsum[GRP];
+#pragma unroll
+        for (int g = 0; g < GRP; g++) lsum[g] = 0.0;
+        for (int t = tid; t < n; t += NT) {
+#pragma unroll
+            for (int g = 0; g < GRP; g++) {
+                const float e = (float)exp((double)__fsub_rn(sc[(size_t)g * maxc + t], M[g]));
+                sc[(size_t)g * maxc + t] = e;          // only this thread touches element t until the barrier below
+                lsum[g] += (double)e;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < GRP; g++) {
+            const double s = warp_sum_d(lsum[g]);
+            if (lane == 0) wsum[warp * GRP + g] = s;
+        }
+        named_bar_sync(barid, NT);
+#pragma unroll
+        for (int g = 0; g < GRP; g++) {
+            double S = 0;
+#pragma unroll
+            for (int w = 0; w < NWARP; w++) S += wsum[w * GRP + g];
+            inv[g] = (float)(1.0 / S);                  // ggml: sum = 1.0/sum in f64, then an f32 scale
+        }
+        for (int t = tid; t < n; t += NT) {
+#pragma unroll
+            for (int g = 0; g < GRP; g++)
+                sc[(size_t)g * maxc + t] = __half2float(__float2half_rn(__fmul_rn(sc[(size_t)g * maxc + t], inv[g])));
+        }
+        named_bar_sync(barid, NT);
     }
-    named_bar_sync(barid, NT);
     stamp(4);
 
     // ---- 3. output dims of this CTA: V columns dotted with the probabilities, lane L = position mod 32 --
-    const int dpc = HD / CL, dbase = (int)rk * dpc;      // HD % (4 * CL) == 0 (checked on the host)
-    for (int d0 = 4 * warp; d0 < dpc; d0 += 4 * NWARP) {
-        float acc[GRP][4];
+    const int dpc = HD / CL, dbase = (int)rk * dpc;      // HD % (8 * CL) == 0 (checked on the host)
+    for (int d0 = 8 * warp; d0 < dpc; d0 += 8 * NWARP) {
+        float acc[GRP][8];
 #pragma unroll
         for (int g = 0; g < GRP; g++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) acc[g][j] = 0.f;
-        constexpr int UV = GRP >= 4 ? 8 : 20;       // V rows in flight per lane
+            for (int j = 0; j < 8; j++) acc[g][j] = 0.f;
+        constexpr int UV = GRP >= 4 ? 4 : 10;       // V rows in flight per lane
         for (int tb = lane; tb < n; tb += 32 * UV) {
-            uint2 vv[UV];
+            uint4 vv[UV];
 #pragma unroll
             for (int u = 0; u < UV; u++) {
                 const int t = min(tb + 32 * u, n - 1);
-                vv[u] = *reinterpret_cast<const uint2*>(v_base + rowoff[t] + dbase + d0);
+                vv[u] = *reinterpret_cast<const uint4*>(v_base + rowoff[t] + dbase + d0);
             }
 #pragma unroll
             for (int u = 0; u < UV; u++) {
                 const int t = tb + 32 * u;
                 if (t < n) {
-                    const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&vv[u].x)), f1 = __half22float2(*reinterpret_cast<const __half2*>(&vv[u].y));
+                    const __half2* h2 = reinterpret_cast<const __half2*>(&vv[u]);
+                    float vf[8];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) { const float2 f = __half22float2(h2[j]); vf[2 * j] = f.x; vf[2 * j + 1] = f.y; }
 #pragma unroll
                     for (int g = 0; g < GRP; g++) {
                         const float p = sc[(size_t)g * maxc + t];
-                        acc[g][0] = fmaf(f0.x, p, acc[g][0]); acc[g][1] = fmaf(f0.y, p, acc[g][1]);
-                        acc[g][2] = fmaf(f1.x, p, acc[g][2]); acc[g][3] = fmaf(f1.y, p, acc[g][3]);
+#pragma unroll
+                        for (int j = 0; j < 8; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
                     }
                 }
             }
         }
 #pragma unroll
         for (int g = 0; g < GRP; g++) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) acc[g][j] = reduce_lanes32(acc[g][j]);
-            if (lane == 0)
-                *reinterpret_cast<float4*>(a.out + ((size_t)kvh * GRP + g) * HD + dbase + d0) = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
+            const float r = reduce8_lanes32(acc[g], lane);
+            if ((lane & 3) == 0) a.out[((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane)] = r;
         }
     }
     stamp(5);
@@ -264,7 +309,7 @@ static inline size_t attn_smem_bytes(int grp, int hd, int max_ctx_pad, int clust
     (void)cluster;
     const int nwarps = nthreads / 32;
     const size_t d = (size_t)((nwarps * grp + 1) & ~1);                                        // doubles
-    const size_t f = (size_t)grp * hd + (size_t)grp * max_ctx_pad + (size_t)nwarps * grp + 2 * grp + (size_t)max_ctx_pad;   // floats + row offsets
+    const size_t f = (size_t)grp * hd + (size_t)grp * max_ctx_pad + (size_t)nwarps * grp + (size_t)max_ctx_pad;   // floats + row offsets
     return (d * sizeof(double) + f * sizeof(float) + 15) / 16 * 16;
 }
 

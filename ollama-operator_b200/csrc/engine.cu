@@ -476,6 +476,7 @@ int Model::setup_mega(Slot& s) {
     MegaLaunch& L = s.mega;
     L = MegaLaunch();
     L.type = type; L.grp = grp; L.head_dim = hp.head_dim; L.cluster = 4;
+    if (const char* v = getenv("B2_MEGA_CLUSTER")) L.cluster = atoi(v);
     for (size_t i = 0; i < s.ops.size(); i++) {
         st[i].kind = s.ops[i].kind;
         if (s.ops[i].kind == 0) {
@@ -528,8 +529,8 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
         a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key; a.grid_count = s.d_grid_count;
         B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
     }
-    if (s.mega_ok && !prof) {
-        B2_TRY(mega_launch(s.mega, stream)); nl++;
+    if (s.mega_ok) {
+        B2_TRY(mega_launch(s.mega, stream)); nl++; B2_TRY(mark(8));
     } else {
         for (const StepOp& op : s.ops) {
             if (op.kind == 0) B2_TRY(gemv_launch(op.g, stream, pdl));
@@ -691,7 +692,7 @@ int Model::profile_step(int seq, int32_t tok, float* class_ms, int* class_launch
     const int rc = enqueue_step(s, true, &nl, &prof);
     use_pdl = saved;
     cudaStreamSynchronize(stream);
-    for (int i = 0; i < 8; i++) { class_ms[i] = 0.f; class_launches[i] = 0; }
+    for (int i = 0; i < 9; i++) { class_ms[i] = 0.f; class_launches[i] = 0; }
     if (rc == B2_OK)
         for (size_t i = 1; i < prof.ev.size(); i++) {
             float ms = 0.f;

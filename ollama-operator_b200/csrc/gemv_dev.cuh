@@ -85,6 +85,16 @@ __device__ __forceinline__ float4 prologue_vals(const GemvArgs& a, const ProStat
     return v;
 }
 
+// amax / 127 correctly rounded without the generic division sequence: one Newton step on a
+// correctly rounded reciprocal is exact division for normal results; tiny inputs take the slow path.
+__device__ __forceinline__ float div127_rn(float a) {
+    if (a < 1e-30f) return __fdiv_rn(a, 127.0f);
+    const float c = 0.007874015718698502f;           // fl(1/127)
+    const float q = __fmul_rn(a, c);
+    const float r = __fmaf_rn(-q, 127.0f, a);         // exact remainder
+    return __fmaf_rn(r, c, q);
+}
+
 __device__ __forceinline__ uint32_t pack4(int a, int b, int c, int d) {
     return (uint32_t)(a & 0xFF) | ((uint32_t)(b & 0xFF) << 8) | ((uint32_t)(c & 0xFF) << 16) | ((uint32_t)(d & 0xFF) << 24);
 }
@@ -103,8 +113,8 @@ static __device__ void prologue_q8_0(const GemvArgs& a, const ProStats& st, uint
         amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 1));
         amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 2));
         amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
-        const float d = __fdiv_rn(amax, 127.0f);
-        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        const float d = div127_rn(amax);
+        const float id = d != 0.0f ? __frcp_rn(d) : 0.0f;
         const int q0 = (int)roundf(__fmul_rn(v.x, id)), q1 = (int)roundf(__fmul_rn(v.y, id));
         const int q2 = (int)roundf(__fmul_rn(v.z, id)), q3 = (int)roundf(__fmul_rn(v.w, id));
         int sum = q0 + q1 + q2 + q3;

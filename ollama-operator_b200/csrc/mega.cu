@@ -246,8 +246,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 2));
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
-                    const float d = __fdiv_rn(amax, 127.0f);
-                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                    const float d = div127_rn(amax);
+                    const float id = d != 0.0f ? __frcp_rn(d) : 0.0f;
                     const int q0 = (int)roundf(__fmul_rn(v.x, id)), q1 = (int)roundf(__fmul_rn(v.y, id));
                     const int q2 = (int)roundf(__fmul_rn(v.z, id)), q3 = (int)roundf(__fmul_rn(v.w, id));
                     int sum = q0 + q1 + q2 + q3;
@@ -444,7 +444,7 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     L.off_xs = (uint32_t)off; off += (size_t)(kq ? k_max / 16 : k_max / 32) * 4; off = (off + 15) / 16 * 16;
     L.off_att = (uint32_t)off;
     L.att_max_local = (max_ctx + 3) / 4 * 4;
-    if (L.head_dim % (4 * L.cluster)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: head_dim %d does not split over a cluster of %d", L.head_dim, L.cluster);
+    if (L.head_dim % (8 * L.cluster)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: head_dim %d does not split over a cluster of %d", L.head_dim, L.cluster);
     off += attndev::attn_smem_bytes(L.grp, L.head_dim, L.att_max_local, L.cluster, MEGA_NCW * 32);
     off = (off + 127) / 128 * 128;
     L.off_ring = (uint32_t)off;

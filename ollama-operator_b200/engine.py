@@ -241,12 +241,12 @@ class Model:
         _check(lib().b2_kv_read(self._h, seq, layer, _ptr(k), _ptr(v), n_tok))
         return k, v
 
-    PROFILE_CLASSES = ("step_begin", "gemv_qkv", "attention", "gemv_wo", "gemv_gate_up", "gemv_down", "gemv_head", "step_end")
+    PROFILE_CLASSES = ("step_begin", "gemv_qkv", "attention", "gemv_wo", "gemv_gate_up", "gemv_down", "gemv_head", "step_end", "persistent_layers")
 
     def profile_step(self, seq: int, tok: int) -> dict:
         """One decode step with per-kernel-class device times: {class: (ms, launches)}."""
-        ms = np.zeros(8, dtype=np.float32)
-        nl = np.zeros(8, dtype=np.int32)
+        ms = np.zeros(9, dtype=np.float32)
+        nl = np.zeros(9, dtype=np.int32)
         _check(lib().b2_profile_step(self._h, seq, tok, _ptr(ms), _ptr(nl)))
         return {c: (float(ms[i]), int(nl[i])) for i, c in enumerate(self.PROFILE_CLASSES)}
 
