@@ -140,6 +140,11 @@ int b2_gemv(int ggml_type, const void* W, int64_t rows, int64_t k, const float* 
  * array: do not let two of them overlap on the GPU. */
 #define B2_NOALLOC_SCRATCH_BYTES (8u << 20)
 int b2_gemv_noalloc(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, const float* gain, float eps, float* y);
+/* ggml mul_mat with n_cols (1..32) activation columns, x [n_cols][k], y [n_cols][rows]: the batched
+ * kernel behind multi-sequence b2_decode and chunked b2_prefill (Q4_0 weights).  Every column equals
+ * b2_gemv on that column bit for bit.  The kernel runs `iters` more times for *ms_out (may be NULL). */
+int b2_gemm(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, int n_cols, const float* gain, float eps, float* y, int iters,
+            float* ms_out);
 /* Same kernel launched `iters` times back to back on resident data; returns the mean device
  * time per launch in *ms_out (CUDA events).  tune = {nb, g, rpg, ns, ctas_per_sm}, zeros for
  * the built-in heuristic. */

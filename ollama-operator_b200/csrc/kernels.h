@@ -135,3 +135,29 @@ struct StepEndArgs {
 int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl);
 
 }  // namespace b2
+
+// ---- batch.cu: several columns (tokens) per weight pass: batched decode and chunked prefill ---------
+namespace b2 {
+constexpr int BATCH_MAX = 32;          // columns per pass (four 8-column MMA tiles)
+// Q8_0-quantised activation columns in global memory: per column two planes of 16 bytes per block
+// (elements 0..15 | 16..31, the layout the GEMV keeps in shared memory), f16-rounded scale, 8*sum(q).
+struct Q8Cols {
+    uint8_t* q = nullptr;      // [BATCH_MAX][2][K/32][16]
+    float* d = nullptr;        // [BATCH_MAX][K/32]
+    int* s8 = nullptr;         // [BATCH_MAX][K/32]
+    int64_t k_cap = 0;         // capacity (elements per column) the strides are computed from
+};
+// x[c] = embedding row of tok[c]; arg-max accumulators cleared
+int batch_begin_launch(const QMat& embd, float* xb, int64_t x_stride, const int* d_tok, unsigned long long* keys, int B, cudaStream_t st);
+// norm (pro) + Q8_0 quantisation of B activation columns x[c*x_stride ..] of length K
+int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pro, const float* gain, const float* nbias, float eps, const Q8Cols& out,
+                      cudaStream_t st);
+// Y[:, c] = epilogue_c(W . q8col_c) for c < B: integer tensor-core MMAs per 32-weight block, exact, with
+// the same per-block float terms and f64 accumulation as the GEMV (bit-identical results per column).
+// colargs: device array [B] of GemvArgs (epilogue operands of each column); pos / page tables per column.
+int gemm_w4a8_launch(const QMat& W, const Q8Cols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride, cudaStream_t st);
+// attention for B columns: d_args[c] describes column c (q, out, page table, position pointer)
+int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& shape, int B, cudaStream_t st);
+// next token of every column from its arg-max accumulator
+int batch_end_launch(const unsigned long long* keys, int* d_next, int B, cudaStream_t st);
+}  // namespace b2

@@ -114,3 +114,22 @@ def test_attention_matches_reference(pkg, oracle, n_ctx, n_head, n_head_kv, hd, 
     # a warp reproduces the SIMD lane order exactly, so the kernel must agree bit for bit for any
     # split of the work over the cluster
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), np.max(np.abs(got - want))
+
+
+@pytest.mark.parametrize("rows,k,n_cols", [(2, 256, 1), (300, 512, 5), (1024, 4096, 32), (258, 11008, 17), (64, 2560 // 256 * 256, 8)])
+def test_batched_gemm_equals_gemv_per_column(pkg, oracle, rows, k, n_cols):
+    """The tensor-core batched kernel must give, column by column, the bits of the GEMV (and of the oracle)."""
+    from gguf import GGMLQuantizationType as T
+    E = pkg.engine
+    rng = np.random.default_rng(rows + k + n_cols)
+    W = pkg.synth.random_blocks(T.Q4_0, rows, k, k ** -0.5, rng)
+    x = rng.standard_normal((n_cols, k)).astype(np.float32)
+    x[0, : k // 2] = 0
+    g = (1 + 0.02 * rng.standard_normal(k)).astype(np.float32)
+    y, _ = E.gemm(E.TYPE_Q4_0, W, rows, k, x)
+    yn, _ = E.gemm(E.TYPE_Q4_0, W, rows, k, x, gain=g, eps=1e-5)
+    for c in range(n_cols):
+        want = oracle.mul_mat_vec(2, W, rows, k, x[c], faithful=2)
+        assert np.array_equal(y[c].view(np.uint32), want.view(np.uint32)), (c, np.abs(y[c] - want).max())
+        wn = oracle.mul_mat_vec(2, W, rows, k, oracle.rms_norm(x[c], g, 1e-5), faithful=2)
+        assert np.array_equal(yn[c].view(np.uint32), wn.view(np.uint32)), c
