@@ -53,7 +53,8 @@ typedef struct {
 } b2_load_opts;
 enum { B2_LOAD_NO_PDL = 1,      /* do not use programmatic dependent launch */
        B2_LOAD_NO_GRAPH = 2,    /* launch kernels one by one instead of replaying CUDA graphs */
-       B2_LOAD_NO_MEGA = 4 };   /* one kernel per matrix instead of the persistent per-step kernel */
+       B2_LOAD_NO_MEGA = 4,     /* one kernel per matrix instead of the persistent per-step kernel */
+       B2_LOAD_NO_BATCH = 8 };  /* evaluate prompts and multi-sequence decode calls one token at a time */
 
 typedef struct {
     int32_t arch;        /* 0 llama, 1 phi2 */

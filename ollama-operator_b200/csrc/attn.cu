@@ -44,6 +44,44 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnArgs
     attn_kv_head<GRP, HD, ATT_THREADS>(a, c, blockIdx.y, smem_raw, threadIdx.x, &xbar, xphase, 1);
 }
 
+// Batched variant: blockIdx.z selects the column (a sequence, or a prompt token of a chunk); each
+// column brings its own query, output, page table and position through a device-resident array.
+template <int GRP, int HD>
+__global__ void __launch_bounds__(ATT_THREADS) attn_decode_batch_kernel(const AttnArgs* __restrict__ args, const AttnCfg c) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t xbar;
+    if (threadIdx.x == 0) {
+        mbar_init(&xbar, c.cluster);
+        mbar_fence_init();
+    }
+    cluster_sync_all();
+    const AttnArgs a = args[blockIdx.z];
+    uint32_t xphase = 0;
+    attn_kv_head<GRP, HD, ATT_THREADS>(a, c, blockIdx.y, smem_raw, threadIdx.x, &xbar, xphase, 1);
+}
+
+template <int GRP, int HD>
+int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg& c, size_t smem, cudaStream_t st) {
+    auto kern = attn_decode_batch_kernel<GRP, HD>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(c.cluster, n_head_kv, B);
+    cfg.blockDim = dim3(ATT_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = c.cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, d_args, c));
+    return B2_OK;
+}
+
 template <int GRP, int HD>
 int launch_grp(const AttnArgs& a, const AttnCfg& c, size_t smem, cudaStream_t st, bool pdl) {
     auto kern = attn_decode_kernel<GRP, HD>;
@@ -95,6 +133,27 @@ int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster
 #undef B2_ATT_CASE
     if (a.head_dim != 64 && a.head_dim != 80 && a.head_dim != 128) B2_FAIL(B2_ERR_UNSUPPORTED, "attn: head_dim %d not supported (64, 80, 128)", a.head_dim);
     B2_FAIL(B2_ERR_UNSUPPORTED, "attn: %d query heads per KV head not supported (1, 2, 4, 8)", grp);
+}
+
+int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& a, int B, cudaStream_t st) {
+    if (a.max_ctx <= 0 || B < 1) B2_FAIL(B2_ERR_ARG, "attn: bad batch arguments");
+    if (a.n_head_kv <= 0 || a.n_head % a.n_head_kv) B2_FAIL(B2_ERR_ARG, "attn: n_head %d not a multiple of n_head_kv %d", a.n_head, a.n_head_kv);
+    const int grp = a.n_head / a.n_head_kv;
+    AttnCfg c;
+    int cluster = 1;      // the columns already spread the work: only small batches split a head over CTAs
+    while (cluster < MAX_CLUSTER && cluster * a.n_head_kv * B * 2 <= 160) cluster *= 2;
+    while (cluster > 1 && a.head_dim % (8 * cluster)) cluster /= 2;
+    c.cluster = cluster;
+    c.max_local = (a.max_ctx + 3) / 4 * 4;
+    const size_t smem = attn_smem_bytes(grp, a.head_dim, c.max_local, cluster, ATT_THREADS);
+    if (smem > 200 * 1024) B2_FAIL(B2_ERR_UNSUPPORTED, "attn: context %d needs %zu B of shared memory", a.max_ctx, smem);
+#define B2_ATT_CASE(G, H) if (grp == G && a.head_dim == H) return launch_grp_batch<G, H>(d_args, a.n_head_kv, B, c, smem, st)
+    B2_ATT_CASE(1, 64); B2_ATT_CASE(1, 80); B2_ATT_CASE(1, 128);
+    B2_ATT_CASE(2, 64); B2_ATT_CASE(2, 80); B2_ATT_CASE(2, 128);
+    B2_ATT_CASE(4, 64); B2_ATT_CASE(4, 80); B2_ATT_CASE(4, 128);
+    B2_ATT_CASE(8, 64); B2_ATT_CASE(8, 80); B2_ATT_CASE(8, 128);
+#undef B2_ATT_CASE
+    B2_FAIL(B2_ERR_UNSUPPORTED, "attn: head_dim %d with %d query heads per KV head not supported", a.head_dim, grp);
 }
 
 }  // namespace b2

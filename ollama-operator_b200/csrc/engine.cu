@@ -76,6 +76,9 @@ Model::~Model() {
     if (kv_k) cudaFree(kv_k);
     if (kv_v) cudaFree(kv_v);
     if (slot_mem) cudaFree(slot_mem);
+    if (bt.mem) cudaFree(bt.mem);
+    if (bt.h_stage) cudaFreeHost(bt.h_stage);
+    if (bt.h_next) cudaFreeHost(bt.h_next);
     if (rope_table) cudaFree(rope_table);
     arena.release();
 }
@@ -180,6 +183,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
     use_pdl = !(flags & B2_LOAD_NO_PDL) && !getenv("B2_NO_PDL");
     use_graph = !(flags & B2_LOAD_NO_GRAPH) && !getenv("B2_NO_GRAPH");
     use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
+    use_batch = !(flags & B2_LOAD_NO_BATCH) && !getenv("B2_NO_BATCH");
 
     const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd, F = hp.n_ff, V = hp.n_vocab;
     if ((nq | nkv | F | V | E) & 1) B2_FAIL(B2_ERR_UNSUPPORTED, "odd matrix dimensions are not supported");
@@ -357,6 +361,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
         build_ops(s);
         B2_TRY(setup_mega(s));
     }
+    if (use_batch) B2_TRY(setup_batch());
     return B2_OK;
 }
 
@@ -616,8 +621,27 @@ int Model::prefill(int seq, const int32_t* toks, int n, float* logits) {
     Slot& s = slots[seq];
     B2_TRY(ensure_pages(s, s.len + n));
     B2_TRY(begin_call());
-    // The prompt is walked with the decode kernels, one token per step (a GEMM-shaped prefill
-    // is the next milestone); prompt tokens are forced from the device-side list.
+    if (bt.ok && n >= batch_min_seqs) {
+        // chunks of up to BATCH_MAX prompt tokens per pass over the weights; only the last token needs the head
+        bt.next_region = 0;
+        int col_slot[BATCH_MAX], col_pos[BATCH_MAX], last_b = 0;
+        for (int t0 = 0; t0 < n; t0 += BATCH_MAX) {
+            const int B = std::min(BATCH_MAX, n - t0);
+            for (int c = 0; c < B; c++) { col_slot[c] = seq; col_pos[c] = s.len + t0 + c; }
+            B2_TRY(batch_step(B, col_slot, col_pos, toks + t0, t0 + B == n ? 1u << (B - 1) : 0u));
+            last_b = B;
+        }
+        if (logits) B2_CUDA(cudaMemcpyAsync(logits, bt.logits + (size_t)(last_b - 1) * hp.n_vocab, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
+        B2_CUDA(cudaMemcpyAsync(bt.h_next, bt.d_next, BATCH_MAX * 4, cudaMemcpyDeviceToHost, stream));
+        B2_TRY(end_call(nullptr));
+        s.host = SeqState{};
+        s.host.cur_tok = bt.h_next[last_b - 1];
+        s.host.pos = s.len + n;
+        s.len += n;
+        return B2_OK;
+    }
+    // Short prompts (and models without batched kernels) walk the prompt with the decode kernels,
+    // one token per step; prompt tokens are forced from the device-side list.
     SeqState st{};
     st.pos = s.len; st.cur_tok = toks[0]; st.n_forced = n - 1; st.forced_idx = 0; st.n_out = 0;
     B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
@@ -639,6 +663,30 @@ int Model::decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* 
         B2_TRY(ensure_pages(slots[seqs[i]], slots[seqs[i]].len + 1));
     }
     B2_TRY(begin_call());
+    if (bt.ok && n_seq >= batch_min_seqs) {
+        bt.next_region = 0;
+        int col_pos[BATCH_MAX];
+        for (int c0 = 0; c0 < n_seq; c0 += BATCH_MAX) {
+            const int B = std::min(BATCH_MAX, n_seq - c0);
+            for (int c = 0; c < B; c++) col_pos[c] = slots[seqs[c0 + c]].len;
+            B2_TRY(batch_step(B, seqs + c0, col_pos, last_tok + c0, B == 32 ? 0xFFFFFFFFu : (1u << B) - 1));
+            if (logits) B2_CUDA(cudaMemcpyAsync(logits + (size_t)c0 * hp.n_vocab, bt.logits, (size_t)B * hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
+            B2_CUDA(cudaMemcpyAsync(bt.h_next, bt.d_next, BATCH_MAX * 4, cudaMemcpyDeviceToHost, stream));
+            {
+                B2_CUDA(cudaStreamSynchronize(stream));        // h_next is reused by the next group
+                for (int c = 0; c < B; c++) {
+                    Slot& s = slots[seqs[c0 + c]];
+                    s.host = SeqState{};
+                    s.host.cur_tok = bt.h_next[c];
+                    s.host.pos = s.len + 1;
+                    if (next_tok) next_tok[c0 + c] = bt.h_next[c];
+                }
+            }
+        }
+        B2_TRY(end_call(nullptr));
+        for (int i = 0; i < n_seq; i++) slots[seqs[i]].len += 1;
+        return B2_OK;
+    }
     for (int i = 0; i < n_seq; i++) {
         Slot& s = slots[seqs[i]];
         SeqState st{};

@@ -60,11 +60,28 @@ struct Slot {
     bool warm_full = false, warm_nohead = false;
 };
 
+// Batched steps (several sequences per decode call, or a chunk of prompt tokens): one set of
+// column buffers for the whole model, per-column operand tables resident on the device.
+struct BatchCtx {
+    bool ok = false;                 // every layer matrix has a batched kernel
+    void* mem = nullptr;
+    float *x = nullptr, *q = nullptr, *att = nullptr, *att2 = nullptr, *h = nullptr, *logits = nullptr;   // [BATCH_MAX][...]
+    Q8Cols q8;
+    int *d_tok = nullptr, *d_pos = nullptr, *d_pt = nullptr, *d_next = nullptr;    // d_pt: [BATCH_MAX][pages_per_seq]
+    unsigned long long* d_keys = nullptr;
+    GemvArgs* d_colargs = nullptr;   // [ops][BATCH_MAX]
+    AttnArgs* d_attargs = nullptr;   // [ops][BATCH_MAX] (attention ops only)
+    std::vector<StepOp> ops;         // the layer pipeline bound to column 0
+    int* h_stage = nullptr;          // pinned upload regions: tok[BATCH_MAX] | pos[BATCH_MAX] | page tables
+    int n_regions = 0, region_ints = 0, next_region = 0;
+    int* h_next = nullptr;           // pinned [BATCH_MAX]
+};
+
 struct StepProfile { std::vector<cudaEvent_t> ev; std::vector<int> cls; };
 
 struct Model {
     HParams hp;
-    bool neox = false, use_pdl = true, use_graph = true, use_mega = true;
+    bool neox = false, use_pdl = true, use_graph = true, use_mega = true, use_batch = true;
     int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
     float2* rope_table = nullptr;     // [max_ctx][n_rot/2]
     Arena arena;
@@ -77,6 +94,8 @@ struct Model {
     std::vector<int> free_pages;
     void* slot_mem = nullptr;
     std::vector<Slot> slots;
+    BatchCtx bt;
+    int batch_min_seqs = 3;           // b2_decode switches to the batched kernels from this many sequences
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     size_t weight_bytes = 0, step_weight_bytes = 0;
@@ -105,6 +124,8 @@ struct Model {
     int ensure_pages(Slot& s, int upto);
     int enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof);
     int run_steps(Slot& s, bool with_head, int n);
+    int setup_batch();
+    int batch_step(int B, const int* col_slot, const int* col_pos, const int32_t* col_tok, uint32_t head_mask);
     int begin_call();
     int end_call(Slot* s);
 };

@@ -1,0 +1,153 @@
+// engine_batch.cu -- batched steps: several sequences per b2_decode call and chunked b2_prefill.
+//
+// llama.cpp evaluates a batch of tokens with the same per-row arithmetic as a single token: every
+// activation row is quantised on its own and every (weight row, activation row) dot product is the
+// same sum of block terms [upstream ggml_compute_forward_mul_mat].  The batched kernels here keep
+// that property bit for bit (tests/test_gpu_model.py compares against the one-token path), so
+// batching is purely a scheduling decision: the weights are streamed once per step for up to
+// BATCH_MAX columns instead of once per token.
+//
+// A "column" is one token being evaluated: in a decode call column c belongs to sequence c of the
+// call; in a prefill chunk the columns are consecutive prompt positions of one sequence, and column
+// c attends to the cache rows the columns before it appended in the same step (the QKV kernel of a
+// layer finishes before its attention kernel starts).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "engine.h"
+
+namespace b2 {
+
+static inline size_t align_up_b(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int Model::setup_batch() {
+    bt.ok = false;
+    if (slots.empty()) return B2_OK;
+    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, F = hp.n_ff, V = hp.n_vocab;
+    int64_t k_max = 0;
+    for (const StepOp& op : slots[0].ops)
+        if (op.kind == 0) {
+            const QMat& W = op.g.W;
+            if (W.type != T_Q4_0 || (W.k % 256) || (W.rows & 1)) return B2_OK;     // per-token path only
+            k_max = std::max(k_max, W.k);
+        }
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { const size_t o2 = align_up_b(off, 256); off = o2 + bytes; return o2; };
+    const size_t o_x = carve((size_t)BATCH_MAX * E * 4), o_q = carve((size_t)BATCH_MAX * nq * 4), o_att = carve((size_t)BATCH_MAX * nq * 4),
+                 o_att2 = carve((size_t)BATCH_MAX * E * 4), o_h = carve((size_t)BATCH_MAX * F * 4), o_logits = carve((size_t)BATCH_MAX * V * 4),
+                 o_q8 = carve((size_t)BATCH_MAX * k_max), o_q8d = carve((size_t)BATCH_MAX * (k_max / 32) * 4),
+                 o_q8s = carve((size_t)BATCH_MAX * (k_max / 32) * 4), o_tok = carve((size_t)(2 * BATCH_MAX + BATCH_MAX * pages_per_seq) * 4),      // tok | pos | page tables: one upload
+                 o_next = carve(BATCH_MAX * 4), o_keys = carve(BATCH_MAX * 8);
+    const size_t n_ops = slots[0].ops.size();
+    const size_t o_cargs = carve(n_ops * BATCH_MAX * sizeof(GemvArgs)), o_aargs = carve(n_ops * BATCH_MAX * sizeof(AttnArgs));
+    B2_CUDA(cudaMalloc(&bt.mem, off));
+    B2_CUDA(cudaMemset(bt.mem, 0, off));
+    uint8_t* b = (uint8_t*)bt.mem;
+    bt.x = (float*)(b + o_x); bt.q = (float*)(b + o_q); bt.att = (float*)(b + o_att); bt.att2 = (float*)(b + o_att2); bt.h = (float*)(b + o_h);
+    bt.logits = (float*)(b + o_logits);
+    bt.q8.q = b + o_q8; bt.q8.d = (float*)(b + o_q8d); bt.q8.s8 = (int*)(b + o_q8s); bt.q8.k_cap = k_max;
+    bt.d_tok = (int*)(b + o_tok); bt.d_pos = bt.d_tok + BATCH_MAX; bt.d_pt = bt.d_tok + 2 * BATCH_MAX; bt.d_next = (int*)(b + o_next);
+    bt.d_keys = (unsigned long long*)(b + o_keys);
+    bt.d_colargs = (GemvArgs*)(b + o_cargs); bt.d_attargs = (AttnArgs*)(b + o_aargs);
+
+    // the pipeline of slot 0 re-bound to the column buffers; per-column operand tables
+    const Slot& s0 = slots[0];
+    bt.ops = s0.ops;
+    std::vector<GemvArgs> ca(n_ops * BATCH_MAX);
+    std::vector<AttnArgs> aa(n_ops * BATCH_MAX);
+    auto rebind = [&](const float* p, int c) -> float* {
+        if (!p) return nullptr;
+        if (p == s0.x) return bt.x + (size_t)c * E;
+        if (p == s0.q) return bt.q + (size_t)c * nq;
+        if (p == s0.att) return bt.att + (size_t)c * nq;
+        if (p == s0.att2) return bt.att2 + (size_t)c * E;
+        if (p == s0.h) return bt.h + (size_t)c * F;
+        return const_cast<float*>(p);
+    };
+    for (size_t i = 0; i < n_ops; i++)
+        for (int c = 0; c < BATCH_MAX; c++) {
+            if (s0.ops[i].kind == 0) {
+                GemvArgs g = s0.ops[i].g;
+                g.x = rebind(g.x, c); g.y = rebind(g.y, c); g.y2 = rebind(g.y2, c);
+                g.kv.page_table = bt.d_pt + (size_t)c * pages_per_seq;
+                g.kv.pos = bt.d_pos + c;
+                ca[i * BATCH_MAX + c] = g;
+                if (c == 0) bt.ops[i].g = g;
+            } else {
+                AttnArgs a = s0.ops[i].a;
+                a.q = rebind(a.q, c); a.out = rebind(a.out, c);
+                a.page_table = bt.d_pt + (size_t)c * pages_per_seq;
+                a.pos = bt.d_pos + c;
+                aa[i * BATCH_MAX + c] = a;
+                if (c == 0) bt.ops[i].a = a;
+            }
+        }
+    B2_CUDA(cudaMemcpy(bt.d_colargs, ca.data(), ca.size() * sizeof(GemvArgs), cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(bt.d_attargs, aa.data(), aa.size() * sizeof(AttnArgs), cudaMemcpyHostToDevice));
+
+    bt.region_ints = 2 * BATCH_MAX + BATCH_MAX * pages_per_seq;
+    bt.n_regions = max_ctx / BATCH_MAX + 4;
+    B2_CUDA(cudaMallocHost(&bt.h_stage, (size_t)bt.n_regions * bt.region_ints * 4));
+    B2_CUDA(cudaMallocHost(&bt.h_next, BATCH_MAX * 4));
+    if (const char* v = getenv("B2_BATCH_MIN")) batch_min_seqs = std::max(1, atoi(v));
+    bt.ok = true;
+    return B2_OK;
+}
+
+// One step for B columns.  col_slot[c] owns the KV pages column c writes to and attends over,
+// col_pos[c] is the cache row it appends, col_tok[c] the token.  Columns whose head_mask bit is set
+// get logits (bt.logits + c * n_vocab) and a greedy next token (bt.d_next[c]).
+int Model::batch_step(int B, const int* col_slot, const int* col_pos, const int32_t* col_tok, uint32_t head_mask) {
+    if (!bt.ok) B2_FAIL(B2_ERR_STATE, "batched kernels are not available for this model");
+    if (B < 1 || B > BATCH_MAX) B2_FAIL(B2_ERR_ARG, "batch_step: %d columns", B);
+    if (bt.next_region >= bt.n_regions) {          // all upload regions of this call are in flight: drain
+        B2_CUDA(cudaStreamSynchronize(stream));
+        bt.next_region = 0;
+    }
+    int* reg = bt.h_stage + (size_t)bt.next_region++ * bt.region_ints;
+    int* h_tok = reg; int* h_pos = reg + BATCH_MAX; int* h_pt = reg + 2 * BATCH_MAX;
+    for (int c = 0; c < B; c++) {
+        const Slot& s = slots[col_slot[c]];
+        h_tok[c] = col_tok[c];
+        h_pos[c] = col_pos[c];
+        memcpy(h_pt + (size_t)c * pages_per_seq, s.pages.data(), s.pages.size() * 4);
+    }
+    // tok, pos and the page tables are contiguous on both sides: one copy
+    B2_CUDA(cudaMemcpyAsync(bt.d_tok, reg, (size_t)(2 * BATCH_MAX + B * pages_per_seq) * 4, cudaMemcpyHostToDevice, stream));
+    int nl = 0;
+    const int E = hp.n_embd;
+    B2_TRY(batch_begin_launch(w_embd, bt.x, E, bt.d_tok, bt.d_keys, B, stream)); nl++;
+    for (size_t i = 0; i < bt.ops.size(); i++) {
+        const StepOp& op = bt.ops[i];
+        if (op.kind == 0) {
+            const GemvArgs& g = op.g;
+            // the same activation vector feeds every segment of a split QKV matrix: quantise once
+            const bool reuse = i > 0 && bt.ops[i - 1].kind == 0 && bt.ops[i - 1].g.x == g.x && bt.ops[i - 1].g.pro == g.pro &&
+                               bt.ops[i - 1].g.gain == g.gain && bt.ops[i - 1].g.W.k == g.W.k && g.epi == EPI_QKV_ROPE;
+            if (!reuse) {
+                B2_TRY(quant_cols_launch(g.x, g.x == bt.x || g.x == bt.att2 ? E : g.x == bt.h ? hp.n_ff : hp.n_head * hp.head_dim, g.W.k, B, g.pro, g.gain,
+                                         g.nbias, g.eps, bt.q8, stream));
+                nl++;
+            }
+            B2_TRY(gemm_w4a8_launch(g.W, bt.q8, B, bt.d_colargs + i * BATCH_MAX, bt.d_pos, bt.d_pt, pages_per_seq, stream)); nl++;
+        } else {
+            B2_TRY(attn_decode_batch_launch(bt.d_attargs + i * BATCH_MAX, op.a, B, stream)); nl++;
+        }
+    }
+    for (int c = 0; c < B; c++)
+        if (head_mask >> c & 1) {
+            GemvArgs h;
+            h.W = w_head; h.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; h.epi = EPI_LOGITS;
+            h.x = bt.x + (size_t)c * E; h.gain = out_norm; h.nbias = out_norm_b; h.eps = hp.norm_eps; h.bias = head_b;
+            h.y = bt.logits + (size_t)c * hp.n_vocab; h.argmax_key = bt.d_keys + c;
+            B2_TRY(gemv_launch(h, stream, false)); nl++;
+        }
+    if (head_mask) { B2_TRY(batch_end_launch(bt.d_keys, bt.d_next, B, stream)); nl++; }
+    launches += nl; last_launches += nl;
+    steps += 1; last_steps += 1;
+    return B2_OK;
+}
+
+}  // namespace b2

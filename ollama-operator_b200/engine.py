@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200gguf.so")
 
 TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0, TYPE_Q4_K, TYPE_Q6_K = 0, 1, 2, 8, 12, 14
-LOAD_NO_PDL, LOAD_NO_GRAPH, LOAD_NO_MEGA = 1, 2, 4
+LOAD_NO_PDL, LOAD_NO_GRAPH, LOAD_NO_MEGA, LOAD_NO_BATCH = 1, 2, 4, 8
 
 # every symbol include/b2gguf.h declares (tests check the library exports all of them)
 SYMBOLS = [

@@ -66,10 +66,10 @@ def test_logits_vs_ggml_generic_order(pkg, oracle, eng, model_dir, preset):
     assert n_same >= 36, n_same
 
 
-@pytest.mark.parametrize("flags", [1, 2, 3, 4, 6, 7])
+@pytest.mark.parametrize("flags", [1, 2, 3, 4, 6, 7, 8, 15])
 def test_logits_match_without_pdl_or_graphs(pkg, oracle, eng, model_dir, flags):
     path = pkg.synth.cached_model("tiny-llama", model_dir)
-    """flags: 1 no PDL, 2 no CUDA graphs, 4 no persistent kernel (one kernel per matrix), and combinations."""
+    """flags: 1 no PDL, 2 no CUDA graphs, 4 no persistent kernel (one kernel per matrix), 8 no batched prompt kernels, and combinations."""
     worst, _ = _teacher_forced_compare(pkg, oracle, eng, path, 5, 6, flags=flags)
     assert worst == 0.0, worst          # every path computes the same bits
 
