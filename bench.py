@@ -67,10 +67,11 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.rows, self.proc = index, [], None
+        self.t0 = self.t1 = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -78,7 +79,13 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def window_begin(self):
+        self.t0 = time.time()
+
+    def window_end(self):
+        self.t1 = time.time()
 
     def stop(self):
         if self.proc:
@@ -87,10 +94,12 @@ class ClockSampler:
                 self.proc.wait(timeout=2)
             except Exception:
                 self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        # samples taken inside the timed regions (the sampler itself starts before the warm-up, nvidia-smi needs ~0.1 s to come up)
+        rows = [r for t, r in self.rows if (self.t0 is None or t >= self.t0) and (self.t1 is None or t <= self.t1 + 0.02)]
+        sm = [float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        reasons = sorted({names[i] for r in rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
                 "samples": len(sm)}
 
@@ -181,15 +190,15 @@ def run_gpu(args):
             torch.cuda.synchronize()
 
     # ---- device-resident loop: `value` ------------------------------------------------------------
-    m.decode_greedy(seq, args.warmup)
     sampler = ClockSampler(local)
-    barrier()
     sampler.start()
+    m.decode_greedy(seq, args.warmup)
+    barrier()
+    sampler.window_begin()
     toks = m.decode_greedy(seq, args.steps)
     st = m.stats()
     barrier()
     gpu_ms, launches = st.gpu_ms, int(st.last_launches)
-    clocks = sampler.stop()
     ctx_mid = args.ctx + args.warmup + args.steps // 2
     # ---- end to end through b2_decode with host buffers: `e2e` ---------------------------------------
     last = int(toks[-1])
@@ -203,6 +212,8 @@ def run_gpu(args):
         e2e_gpu_ms += m.stats().gpu_ms
     barrier()
     e2e_s = time.perf_counter() - t0
+    sampler.window_end()
+    clocks = sampler.stop()       # samples span both timed regions (device-resident loop and end-to-end loop)
 
     tmax = torch.tensor([gpu_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
     if dist:
@@ -255,15 +266,47 @@ def run_gpu(args):
                      "peak_source": peak_src,
                      "step": {"bytes": step_bytes, "achieved": step_gbs, "frac": step_gbs / peak}},
         "profile_step_ms": {k: round(v, 4) for k, v in prof_ms.items() if v > 0},
-        "prefill": {"tokens": args.ctx, "ms": prefill_ms, "note": "token-by-token through the decode kernels"},
+        "prefill": {"tokens": args.ctx, "ms": prefill_ms, "tok_s": args.ctx / (prefill_ms * 1e-3),
+                    "note": "chunks of 32 tokens per weight pass through the batched W4A8 kernel (bit-identical to token-by-token)"},
         "setup_s": {"write_gguf": round(gen_s, 1), "load": round(load_s, 1)},
     }
     if world == 1 and not args.no_cpu:
         out["cpu_baseline"], out["parity"] = cpu_baseline(args, p, m, seq, path, cfg)
-    m.close(); eng.close()
+    m.close()
+    if world == 1 and not args.no_batch:
+        out["batch32"] = batch_decode(args, p, eng, path, info)
+    eng.close()
     if dist:
         dist.destroy_process_group()
     print(json.dumps(out))
+
+
+def batch_decode(args, p, eng, path, info, n_seq=32, steps=16):
+    """BASELINE.json configs[1], second half: 32 sequences (different prompts) decoded together
+    through b2_decode with host token buffers, after a prefill of args.ctx tokens each."""
+    m = eng.load(path, max_batch=n_seq, max_ctx=args.ctx + steps + 8)
+    seqs, tok = [], []
+    pre_ms = 0.0
+    for i in range(n_seq):
+        s = m.seq_new()
+        lg = m.prefill(s, p.synth.prompt_tokens(args.ctx, info.n_vocab, seed=4000 + i))
+        pre_ms += m.stats().gpu_ms
+        seqs.append(s); tok.append(int(np.argmax(lg)))
+    for _ in range(3):
+        tok = [int(t) for t in m.decode(seqs, tok)]
+    t0 = time.perf_counter()
+    gpu_ms = 0.0
+    for _ in range(steps):
+        tok = [int(t) for t in m.decode(seqs, tok)]
+        gpu_ms += m.stats().gpu_ms
+    wall = time.perf_counter() - t0
+    ctx_mid = args.ctx + 3 + steps // 2
+    step_bytes = info.step_weight_bytes + n_seq * ctx_mid * info.kv_bytes_per_token
+    m.close()
+    peak, _ = peaks()
+    return {"n_seq": n_seq, "steps": steps, "tok_s": n_seq * steps / wall, "ms_per_step": wall / steps * 1e3, "gpu_ms_per_step": gpu_ms / steps,
+            "prefill_tok_s": n_seq * args.ctx / (pre_ms * 1e-3), "step_bytes": step_bytes,
+            "hbm_frac": step_bytes / (gpu_ms / steps * 1e-3) / 1e9 / peak}
 
 
 def cpu_baseline(args, p, m, seq, path, cfg):
@@ -313,6 +356,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="llama2-7b")
     ap.add_argument("--ctx", type=int, default=512)
+    ap.add_argument("--no-batch", action="store_true", help="skip the 32-sequence decode measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
