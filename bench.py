@@ -254,6 +254,13 @@ def run_gpu(args):
         k_bytes = rows_up * cfg.n_embd * bpw
         k_name = f"gemv_kernel gate|up {rows_up}x{cfg.n_embd}"
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    traffic = None            # DRAM bytes of one launch of that kernel from the committed ncu capture (same model, shorter context)
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tr["kernel"] in k_name and args.model == "llama2-7b":
+            traffic = tr["dram_bytes_per_launch"] + (m.seq_len(seq) - tr["context"]) * info.kv_bytes_per_token
+    except (OSError, KeyError, ValueError):
+        pass
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": gpu_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -261,7 +268,7 @@ def run_gpu(args):
         "clocks": clocks, "gpu_launches": launches,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4,
                 "gpu_ms_per_step": e2e_gpu_ms / args.steps},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": k_name, "bytes_per_launch": k_bytes, "ms_per_launch": k_ms,
                      "peak_source": peak_src,
                      "step": {"bytes": step_bytes, "achieved": step_gbs, "frac": step_gbs / peak}},

@@ -372,13 +372,16 @@ int b2_gemm(int ggml_type, const void* W, int64_t rows, int64_t k, const float* 
     QMat m;
     B2_TRY(src.alloc(nbytes)); B2_TRY(dx.alloc((size_t)n_cols * k * 4)); B2_TRY(dg.alloc((size_t)k * 4)); B2_TRY(dy.alloc((size_t)n_cols * rows * 4));
     B2_TRY(alloc_qmat(m, planes, ggml_type, rows, k));
-    B2_TRY(dq.alloc((size_t)BATCH_MAX * k)); B2_TRY(dd.alloc((size_t)BATCH_MAX * (k / 32) * 4)); B2_TRY(ds.alloc((size_t)BATCH_MAX * (k / 32) * 4));
+    B2_TRY(dq.alloc(q8cols_q_bytes(k))); B2_TRY(dd.alloc(q8cols_d_bytes(k))); B2_TRY(ds.alloc(q8cols_d_bytes(k)));
+    B2_CUDA(cudaMemset(dq.p, 0, q8cols_q_bytes(k))); B2_CUDA(cudaMemset(dd.p, 0, q8cols_d_bytes(k))); B2_CUDA(cudaMemset(ds.p, 0, q8cols_d_bytes(k)));
     B2_TRY(dargs.alloc(sizeof(GemvArgs) * BATCH_MAX)); B2_TRY(dpos.alloc(BATCH_MAX * 4)); B2_TRY(dpt.alloc(BATCH_MAX * 4));
     B2_CUDA(cudaMemset(dpos.p, 0, BATCH_MAX * 4)); B2_CUDA(cudaMemset(dpt.p, 0, BATCH_MAX * 4));
     B2_CUDA(cudaMemcpy(src.p, W, nbytes, cudaMemcpyHostToDevice));
     B2_CUDA(cudaMemcpy(dx.p, x, (size_t)n_cols * k * 4, cudaMemcpyHostToDevice));
     if (gain) B2_CUDA(cudaMemcpy(dg.p, gain, (size_t)k * 4, cudaMemcpyHostToDevice));
     B2_TRY(repack(ggml_type, src.p, rows, k, m, 0, 1, 0));
+    GemmMaps maps;
+    B2_TRY(gemm_make_maps(m, &maps));
     std::vector<GemvArgs> ca(n_cols);
     for (int c = 0; c < n_cols; c++) { ca[c].epi = EPI_STORE; ca[c].y = dy.as<float>() + (size_t)c * rows; }
     B2_CUDA(cudaMemcpy(dargs.p, ca.data(), sizeof(GemvArgs) * n_cols, cudaMemcpyHostToDevice));
@@ -387,9 +390,9 @@ int b2_gemm(int ggml_type, const void* W, int64_t rows, int64_t k, const float* 
     cudaEvent_t e0, e1;
     B2_CUDA(cudaEventCreate(&e0)); B2_CUDA(cudaEventCreate(&e1));
     const int n = iters > 0 ? iters : 1;
-    B2_TRY(gemm_w4a8_launch(m, q8, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0));
+    B2_TRY(gemm_w4a8_launch(m, maps, q8, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0));
     cudaEventRecord(e0, 0);
-    for (int i = 0; i < n; i++) B2_TRY(gemm_w4a8_launch(m, q8, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0));
+    for (int i = 0; i < n; i++) B2_TRY(gemm_w4a8_launch(m, maps, q8, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0));
     cudaEventRecord(e1, 0);
     B2_CUDA(cudaDeviceSynchronize());
     float ms = 0;

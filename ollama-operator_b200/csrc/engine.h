@@ -72,6 +72,7 @@ struct BatchCtx {
     GemvArgs* d_colargs = nullptr;   // [ops][BATCH_MAX]
     AttnArgs* d_attargs = nullptr;   // [ops][BATCH_MAX] (attention ops only)
     std::vector<StepOp> ops;         // the layer pipeline bound to column 0
+    std::vector<GemmMaps> maps;      // TMA descriptors of every matrix of the pipeline
     int* h_stage = nullptr;          // pinned upload regions: tok[BATCH_MAX] | pos[BATCH_MAX] | page tables
     int n_regions = 0, region_ints = 0, next_region = 0;
     int* h_next = nullptr;           // pinned [BATCH_MAX]

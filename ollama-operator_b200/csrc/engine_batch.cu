@@ -30,15 +30,14 @@ int Model::setup_batch() {
     for (const StepOp& op : slots[0].ops)
         if (op.kind == 0) {
             const QMat& W = op.g.W;
-            if (W.type != T_Q4_0 || (W.k % 256) || (W.rows & 1)) return B2_OK;     // per-token path only
+            if (!gemm_supported(W)) return B2_OK;     // per-token path only
             k_max = std::max(k_max, W.k);
         }
     size_t off = 0;
     auto carve = [&](size_t bytes) { const size_t o2 = align_up_b(off, 256); off = o2 + bytes; return o2; };
     const size_t o_x = carve((size_t)BATCH_MAX * E * 4), o_q = carve((size_t)BATCH_MAX * nq * 4), o_att = carve((size_t)BATCH_MAX * nq * 4),
                  o_att2 = carve((size_t)BATCH_MAX * E * 4), o_h = carve((size_t)BATCH_MAX * F * 4), o_logits = carve((size_t)BATCH_MAX * V * 4),
-                 o_q8 = carve((size_t)BATCH_MAX * k_max), o_q8d = carve((size_t)BATCH_MAX * (k_max / 32) * 4),
-                 o_q8s = carve((size_t)BATCH_MAX * (k_max / 32) * 4), o_tok = carve((size_t)(2 * BATCH_MAX + BATCH_MAX * pages_per_seq) * 4),      // tok | pos | page tables: one upload
+                 o_q8 = carve(q8cols_q_bytes(k_max)), o_q8d = carve(q8cols_d_bytes(k_max)), o_q8s = carve(q8cols_d_bytes(k_max)), o_tok = carve((size_t)(2 * BATCH_MAX + BATCH_MAX * pages_per_seq) * 4),      // tok | pos | page tables: one upload
                  o_next = carve(BATCH_MAX * 4), o_keys = carve(BATCH_MAX * 8);
     const size_t n_ops = slots[0].ops.size();
     const size_t o_cargs = carve(n_ops * BATCH_MAX * sizeof(GemvArgs)), o_aargs = carve(n_ops * BATCH_MAX * sizeof(AttnArgs));
@@ -84,6 +83,9 @@ int Model::setup_batch() {
                 if (c == 0) bt.ops[i].a = a;
             }
         }
+    bt.maps.resize(n_ops);
+    for (size_t i = 0; i < n_ops; i++)
+        if (s0.ops[i].kind == 0) B2_TRY(gemm_make_maps(s0.ops[i].g.W, &bt.maps[i]));
     B2_CUDA(cudaMemcpy(bt.d_colargs, ca.data(), ca.size() * sizeof(GemvArgs), cudaMemcpyHostToDevice));
     B2_CUDA(cudaMemcpy(bt.d_attargs, aa.data(), aa.size() * sizeof(AttnArgs), cudaMemcpyHostToDevice));
 
@@ -131,7 +133,7 @@ int Model::batch_step(int B, const int* col_slot, const int* col_pos, const int3
                                          g.nbias, g.eps, bt.q8, stream));
                 nl++;
             }
-            B2_TRY(gemm_w4a8_launch(g.W, bt.q8, B, bt.d_colargs + i * BATCH_MAX, bt.d_pos, bt.d_pt, pages_per_seq, stream)); nl++;
+            B2_TRY(gemm_w4a8_launch(g.W, bt.maps[i], bt.q8, B, bt.d_colargs + i * BATCH_MAX, bt.d_pos, bt.d_pt, pages_per_seq, stream)); nl++;
         } else {
             B2_TRY(attn_decode_batch_launch(bt.d_attargs + i * BATCH_MAX, op.a, B, stream)); nl++;
         }

@@ -104,8 +104,11 @@ __device__ __forceinline__ uint32_t pack4(int a, int b, int c, int d) {
 // Shared layout: xq = two planes of 16 B per block (elements 0..15 | 16..31) so that the
 // per-lane LDS.128 of the main loop is conflict-free; xd[b] = f16-rounded d; xs[b] = 8*sum(q)
 // (folds Q4_0's -8 offset: sum (w-8) q = sum w q - 8 sum q, exactly, in integers).
-static __device__ void prologue_q8_0(const GemvArgs& a, const ProStats& st, uint8_t* xq, float* xd, int* xs, int tid, int ntc) {
-    const int K = (int)a.W.k, nbk = K / 32;
+// The quantiser proper: store(block, offset in block (multiple of 4), four packed int8, f16-rounded scale, 8*sum(q));
+// scale and sum are valid for offset 0 only.
+template <class Store>
+static __device__ __forceinline__ void prologue_q8_0_each(const GemvArgs& a, const ProStats& st, int tid, int ntc, Store store) {
+    const int K = (int)a.W.k;
     const unsigned lane = tid & 31, gmask = 0xFFu << (lane & ~7u);
     for (int i = tid * 4; i < K; i += ntc * 4) {
         const float4 v = prologue_vals(a, st, i);
@@ -121,14 +124,15 @@ static __device__ void prologue_q8_0(const GemvArgs& a, const ProStats& st, uint
         sum += __shfl_xor_sync(gmask, sum, 1);
         sum += __shfl_xor_sync(gmask, sum, 2);
         sum += __shfl_xor_sync(gmask, sum, 4);
-        const int b = i >> 5, o = i & 31;
-        uint8_t* dst = xq + (o < 16 ? 0 : nbk * 16) + b * 16 + (o & 15);
-        *reinterpret_cast<uint32_t*>(dst) = pack4(q0, q1, q2, q3);
-        if (o == 0) {
-            xd[b] = __half2float(__float2half_rn(d));
-            xs[b] = 8 * sum;
-        }
+        store(i >> 5, i & 31, pack4(q0, q1, q2, q3), __half2float(__float2half_rn(d)), 8 * sum);
     }
+}
+static __device__ void prologue_q8_0(const GemvArgs& a, const ProStats& st, uint8_t* xq, float* xd, int* xs, int tid, int ntc) {
+    const int nbk = (int)a.W.k / 32;
+    prologue_q8_0_each(a, st, tid, ntc, [=](int b, int o, uint32_t w, float d, int s8) {
+        *reinterpret_cast<uint32_t*>(xq + (o < 16 ? 0 : nbk * 16) + b * 16 + (o & 15)) = w;
+        if (o == 0) { xd[b] = d; xs[b] = s8; }
+    });
 }
 
 // Q8_K (quantize_row_q8_K_ref): per 256: iscale = -127/max (max = signed value of largest

@@ -1,5 +1,6 @@
 // kernels.h -- internal interface between the engine (host C++) and the CUDA kernels.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -136,17 +137,26 @@ int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl);
 
 }  // namespace b2
 
-// ---- batch.cu: several columns (tokens) per weight pass: batched decode and chunked prefill ---------
+// ---- batch.cu / gemm.cu: several columns (tokens) per weight pass: batched decode and chunked prefill ----
 namespace b2 {
 constexpr int BATCH_MAX = 32;          // columns per pass (four 8-column MMA tiles)
-// Q8_0-quantised activation columns in global memory: per column two planes of 16 bytes per block
-// (elements 0..15 | 16..31, the layout the GEMV keeps in shared memory), f16-rounded scale, 8*sum(q).
+constexpr int GEMM_KC = 16;            // 32-weight blocks per K chunk (one pipeline stage of the batched kernel)
+constexpr int GEMM_XCOL = 2 * GEMM_KC * 16 + 16;   // bytes of one column's K chunk, padded (conflict-free B-fragment loads)
+// Q8_0-quantised activation columns in global memory, chunk-major so that one K chunk of all columns
+// is one contiguous range already in the batched kernel's shared-memory layout:
+//   q  [n_chunks][BATCH_MAX][GEMM_XCOL]: per column and chunk two planes of 16 bytes per block
+//                                         (elements 0..15 | 16..31 of each block), then 16 bytes of padding
+//   d  [n_chunks][GEMM_KC][BATCH_MAX]:   f16-rounded scales;  s8: same shape, -8 * sum(q) per block
 struct Q8Cols {
-    uint8_t* q = nullptr;      // [BATCH_MAX][2][K/32][16]
-    float* d = nullptr;        // [BATCH_MAX][K/32]
-    int* s8 = nullptr;         // [BATCH_MAX][K/32]
-    int64_t k_cap = 0;         // capacity (elements per column) the strides are computed from
+    uint8_t* q = nullptr;
+    float* d = nullptr;
+    int* s8 = nullptr;
+    int64_t k_cap = 0;         // capacity in elements per column
 };
+inline int64_t q8cols_chunks(int64_t k) { return (k / 32 + GEMM_KC - 1) / GEMM_KC; }
+inline size_t q8cols_q_bytes(int64_t k) { return (size_t)q8cols_chunks(k) * BATCH_MAX * GEMM_XCOL; }
+inline size_t q8cols_d_bytes(int64_t k) { return (size_t)q8cols_chunks(k) * GEMM_KC * BATCH_MAX * 4; }
+struct alignas(64) GemmMaps { CUtensorMap q, d; };     // TMA descriptors of one Q4_0 matrix: nibble plane, scale plane
 // x[c] = embedding row of tok[c]; arg-max accumulators cleared
 int batch_begin_launch(const QMat& embd, float* xb, int64_t x_stride, const int* d_tok, unsigned long long* keys, int B, cudaStream_t st);
 // norm (pro) + Q8_0 quantisation of B activation columns x[c*x_stride ..] of length K
@@ -155,7 +165,10 @@ int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pr
 // Y[:, c] = epilogue_c(W . q8col_c) for c < B: integer tensor-core MMAs per 32-weight block, exact, with
 // the same per-block float terms and f64 accumulation as the GEMV (bit-identical results per column).
 // colargs: device array [B] of GemvArgs (epilogue operands of each column); pos / page tables per column.
-int gemm_w4a8_launch(const QMat& W, const Q8Cols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride, cudaStream_t st);
+bool gemm_supported(const QMat& W);
+int gemm_make_maps(const QMat& W, GemmMaps* out);
+int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride,
+                     cudaStream_t st);
 // attention for B columns: d_args[c] describes column c (q, out, page table, position pointer)
 int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& shape, int B, cudaStream_t st);
 // next token of every column from its arg-max accumulator
