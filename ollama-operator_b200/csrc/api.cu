@@ -2,6 +2,8 @@
 #include <string.h>
 
 #include <new>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "engine.h"
@@ -11,7 +13,15 @@ struct b2_ctx {
 };
 struct b2_model {
     b2_ctx* ctx = nullptr;
-    b2::Model m;
+    b2::Model m;                       // the model, or shard 0 of a tensor-parallel group
+    std::vector<b2::Model*> peers;     // shards 1 .. tp_size-1, one per GPU
+    ~b2_model() {
+        for (size_t i = 0; i < peers.size(); i++) {
+            cudaSetDevice(ctx->devs[i + 1]);
+            delete peers[i];
+        }
+        cudaSetDevice(ctx->devs[0]);
+    }
 };
 
 using namespace b2;
@@ -45,6 +55,37 @@ int alloc_qmat(QMat& m, DevBuf planes[4], int type, int64_t rows, int64_t k) {
         B2_CUDA(cudaMemset(planes[p].p, 0, (size_t)rows * m.stride[p]));
         m.plane[p] = planes[p].as<uint8_t>();
     }
+    return B2_OK;
+}
+
+// Run `f(shard, rank)` on every shard of the model: shard 0 on the calling thread, the others on their
+// own threads (each shard's kernels wait for its peers inside the all-reduce, so the shards must be
+// driven concurrently).  Returns the first failure, with its message.
+template <class F>
+int tp_call(b2_model* m, F f) {
+    if (!m) B2_FAIL(B2_ERR_ARG, "null model");
+    const int n = 1 + (int)m->peers.size();
+    if (n == 1) {
+        B2_CUDA(cudaSetDevice(m->ctx->devs[0]));
+        return f(m->m, 0);
+    }
+    std::vector<int> rc(n, 0);
+    std::vector<std::string> err(n);
+    std::vector<std::thread> th;
+    for (int r = 1; r < n; r++)
+        th.emplace_back([&, r] {
+            if (cudaSetDevice(m->ctx->devs[r]) != cudaSuccess) { rc[r] = B2_ERR_CUDA; err[r] = "cudaSetDevice failed"; return; }
+            rc[r] = f(*m->peers[r - 1], r);
+            if (rc[r] != B2_OK) err[r] = last_error();
+        });
+    if (cudaSetDevice(m->ctx->devs[0]) != cudaSuccess) { rc[0] = B2_ERR_CUDA; err[0] = "cudaSetDevice failed"; }
+    else {
+        rc[0] = f(m->m, 0);
+        if (rc[0] != B2_OK) err[0] = last_error();
+    }
+    for (auto& t : th) t.join();
+    for (int r = 0; r < n; r++)
+        if (rc[r] != B2_OK) { set_error("%s", err[r].c_str()); return rc[r]; }
     return B2_OK;
 }
 
@@ -90,7 +131,20 @@ int b2_model_load(b2_ctx* ctx, const char* gguf_path, const b2_load_opts* opts, 
     b2_model* m = new (std::nothrow) b2_model;
     if (!m) B2_FAIL(B2_ERR_NOMEM, "out of host memory");
     m->ctx = ctx;
-    const int rc = m->m.load(gguf_path, opts);
+    const int tp = opts && opts->tp_size > 1 ? opts->tp_size : 1;
+    if (tp > TP_MAX || tp > (int)ctx->devs.size()) {
+        delete m;
+        B2_FAIL(B2_ERR_ARG, "b2_model_load: tp_size=%d needs that many devices in b2_init (have %d, at most %d)", tp, (int)ctx->devs.size(), TP_MAX);
+    }
+    for (int r = 1; r < tp; r++) m->peers.push_back(new b2::Model);
+    // every shard reads its slices of the file on its own thread
+    int rc = tp_call(m, [&](Model& s, int r) { return s.load(gguf_path, opts, r, tp); });
+    if (rc == B2_OK && tp > 1) {
+        std::vector<Model*> all{&m->m};
+        for (Model* p : m->peers) all.push_back(p);
+        for (int r = 0; r < tp && rc == B2_OK; r++) rc = all[r]->tp_connect(all.data());
+        cudaSetDevice(ctx->devs[0]);
+    }
     if (rc != B2_OK) { delete m; return rc; }
     *out = m;
     return B2_OK;
@@ -109,7 +163,8 @@ int b2_model_get_info(const b2_model* m, b2_model_info* info) {
     info->arch = h.arch; info->n_layer = h.n_layer; info->n_embd = h.n_embd; info->n_head = h.n_head; info->n_head_kv = h.n_head_kv;
     info->head_dim = h.head_dim; info->n_ff = h.n_ff; info->n_vocab = h.n_vocab; info->n_ctx = h.n_ctx; info->n_rot = h.n_rot;
     info->max_batch = m->m.max_batch; info->max_ctx = m->m.max_ctx; info->norm_eps = h.norm_eps; info->rope_freq_base = h.rope_freq_base;
-    info->weight_bytes = m->m.weight_bytes; info->step_weight_bytes = m->m.step_weight_bytes;
+    info->weight_bytes = m->m.weight_bytes; info->step_weight_bytes = m->m.step_weight_bytes;     // per GPU under tensor parallelism
+    for (const Model* p : m->peers) { info->weight_bytes += p->weight_bytes; info->step_weight_bytes += p->step_weight_bytes; }
     info->kv_bytes_per_token = (uint64_t)h.n_layer * 2 * h.n_head_kv * h.head_dim * 2;
     return B2_OK;
 }
@@ -123,27 +178,47 @@ int b2_model_get_info(const b2_model* m, b2_model_info* info) {
 
 int b2_seq_new(b2_model* m, int* seq_out) {
     if (!seq_out) B2_FAIL(B2_ERR_ARG, "b2_seq_new: null out pointer");
-    B2_MODEL_CALL(m, m->m.seq_new(seq_out));
+    return tp_call(m, [&](Model& s, int r) { int dummy; return s.seq_new(r == 0 ? seq_out : &dummy); });      // every shard hands out the same slot
 }
-int b2_seq_free(b2_model* m, int seq) { B2_MODEL_CALL(m, m->m.seq_free(seq)); }
+int b2_seq_free(b2_model* m, int seq) { return tp_call(m, [&](Model& s, int) { return s.seq_free(seq); }); }
 int b2_seq_len(const b2_model* m, int seq) {
     if (!m) B2_FAIL(B2_ERR_ARG, "null model");
     B2_TRY(m->m.check_seq(seq));
     return m->m.slots[seq].len;
 }
-int b2_seq_truncate(b2_model* m, int seq, int n_keep) { B2_MODEL_CALL(m, m->m.seq_truncate(seq, n_keep)); }
-int b2_prefill(b2_model* m, int seq, const int32_t* toks, int n, float* logits) { B2_MODEL_CALL(m, m->m.prefill(seq, toks, n, logits)); }
+int b2_seq_truncate(b2_model* m, int seq, int n_keep) { return tp_call(m, [&](Model& s, int) { return s.seq_truncate(seq, n_keep); }); }
+int b2_prefill(b2_model* m, int seq, const int32_t* toks, int n, float* logits) {
+    return tp_call(m, [&](Model& s, int r) { return s.prefill(seq, toks, n, r == 0 ? logits : nullptr); });
+}
 int b2_decode(b2_model* m, int n_seq, const int* seqs, const int32_t* last_tok, int32_t* next_tok, float* logits) {
-    B2_MODEL_CALL(m, m->m.decode(n_seq, seqs, last_tok, next_tok, logits));
+    return tp_call(m, [&](Model& s, int r) { return s.decode(n_seq, seqs, last_tok, r == 0 ? next_tok : nullptr, r == 0 ? logits : nullptr); });
 }
 int b2_decode_greedy(b2_model* m, int seq, int32_t first_tok, int n_steps, int32_t* out_toks) {
-    B2_MODEL_CALL(m, m->m.decode_greedy(seq, first_tok, n_steps, out_toks));
+    return tp_call(m, [&](Model& s, int r) { return s.decode_greedy(seq, first_tok, n_steps, r == 0 ? out_toks : nullptr); });
 }
 int b2_kv_read(b2_model* m, int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok) {
-    B2_MODEL_CALL(m, m->m.kv_read(seq, layer, k_out, v_out, n_tok));
+    if (!m) B2_FAIL(B2_ERR_ARG, "null model");
+    if (m->peers.empty()) B2_MODEL_CALL(m, m->m.kv_read(seq, layer, k_out, v_out, n_tok));
+    // tensor parallel: every shard holds its KV heads; stitch the rows together
+    if (n_tok < 0) B2_FAIL(B2_ERR_ARG, "kv_read: n_tok %d", n_tok);
+    const int tp = 1 + (int)m->peers.size();
+    const size_t w = (size_t)m->m.n_head_kv_l * m->m.hp.head_dim;
+    std::vector<uint16_t> kt(w * n_tok), vt(w * n_tok);
+    for (int r = 0; r < tp; r++) {
+        Model& s = r == 0 ? m->m : *m->peers[r - 1];
+        B2_CUDA(cudaSetDevice(m->ctx->devs[r]));
+        B2_TRY(s.kv_read(seq, layer, k_out ? kt.data() : nullptr, v_out ? vt.data() : nullptr, n_tok));
+        for (int t = 0; t < n_tok; t++) {
+            if (k_out) memcpy(k_out + ((size_t)t * tp + r) * w, kt.data() + (size_t)t * w, w * 2);
+            if (v_out) memcpy(v_out + ((size_t)t * tp + r) * w, vt.data() + (size_t)t * w, w * 2);
+        }
+    }
+    cudaSetDevice(m->ctx->devs[0]);
+    return B2_OK;
 }
 int b2_profile_step(b2_model* m, int seq, int32_t tok, float* class_ms, int* class_launches) {
-    B2_MODEL_CALL(m, m->m.profile_step(seq, tok, class_ms, class_launches));
+    float ms[9]; int nl[9];
+    return tp_call(m, [&](Model& s, int r) { return s.profile_step(seq, tok, r == 0 ? class_ms : ms, r == 0 ? class_launches : nl); });
 }
 int b2_debug_read(b2_model* m, int seq, int what, float* out, int n) {
     if (!m || !out) B2_FAIL(B2_ERR_ARG, "b2_debug_read: null argument");

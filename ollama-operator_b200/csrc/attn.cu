@@ -63,11 +63,8 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_batch_kernel(const At
 template <int GRP, int HD>
 int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg& c, size_t smem, cudaStream_t st) {
     auto kern = attn_decode_batch_kernel<GRP, HD>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static PerDeviceSmem configured;
+    if (configured.raise(smem)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(c.cluster, n_head_kv, B);
     cfg.blockDim = dim3(ATT_THREADS);
@@ -85,11 +82,8 @@ int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg
 template <int GRP, int HD>
 int launch_grp(const AttnArgs& a, const AttnCfg& c, size_t smem, cudaStream_t st, bool pdl) {
     auto kern = attn_decode_kernel<GRP, HD>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static PerDeviceSmem configured;
+    if (configured.raise(smem)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(c.cluster, a.n_head_kv, 1);
     cfg.blockDim = dim3(ATT_THREADS);

@@ -36,6 +36,19 @@ const char* last_error();
         return (code);               \
     } while (0)
 
+// Function attributes (dynamic shared memory limit) are per device: remember what was set where.
+struct PerDeviceSmem {
+    size_t v[64] = {};
+    bool raise(size_t smem) {          // true if the attribute must be (re)set on the current device
+        int d = 0;
+        cudaGetDevice(&d);
+        d &= 63;
+        if (smem <= v[d]) return false;
+        v[d] = smem;
+        return true;
+    }
+};
+
 // ---- device helpers -------------------------------------------------------------------
 #ifdef __CUDACC__
 

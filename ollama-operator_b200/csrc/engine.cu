@@ -76,6 +76,7 @@ Model::~Model() {
     if (kv_k) cudaFree(kv_k);
     if (kv_v) cudaFree(kv_v);
     if (slot_mem) cudaFree(slot_mem);
+    if (tp_mem) cudaFree(tp_mem);
     if (bt.mem) cudaFree(bt.mem);
     if (bt.h_stage) cudaFreeHost(bt.h_stage);
     if (bt.h_next) cudaFreeHost(bt.h_next);
@@ -105,6 +106,16 @@ int Model::upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat
     B2_CUDA(cudaMemcpyAsync(staging, t->data + (size_t)src_row0 * rb, (size_t)rows * rb, cudaMemcpyHostToDevice, stream));
     B2_TRY(repack(t->type, staging, rows, k, dst, dst_row0, dst_row_step, stream));
     B2_CUDA(cudaStreamSynchronize(stream));     // staging is reused by the next tensor
+    return B2_OK;
+}
+// Tensor-parallel K slice: columns [k0, k0 + kl) of every row (whole blocks), gathered by a strided copy
+int Model::upload_quant_kslice(const GgufTensor* t, int64_t rows, int64_t k_full, int64_t k0, int64_t kl, const QMat& dst) {
+    const int be = type_block_elems(t->type);
+    if (k0 % be || kl % be) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor-parallel split of K=%lld at %lld does not fall on a %d-element block boundary", (long long)k_full, (long long)k0, be);
+    const size_t rb_full = type_row_bytes(t->type, k_full), rb = type_row_bytes(t->type, kl), off = type_row_bytes(t->type, k0);
+    B2_CUDA(cudaMemcpy2DAsync(staging, rb, t->data + off, rb_full, rb, (size_t)rows, cudaMemcpyHostToDevice, stream));
+    B2_TRY(repack(t->type, staging, rows, kl, dst, 0, 1, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
     return B2_OK;
 }
 int Model::upload_f32(const GgufFile& f, const std::string& name, int64_t n, float** out, bool optional) {
@@ -139,7 +150,9 @@ int Model::upload_rows_headwise(const GgufTensor* t, int64_t n_heads, int64_t k,
     return B2_OK;
 }
 
-int Model::load(const char* path, const b2_load_opts* o) {
+int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
+    tp_rank = rank; tp_size = size;
+    B2_CUDA(cudaGetDevice(&device));
     GgufFile f;
     B2_TRY(f.open(path));
     std::string arch;
@@ -178,14 +191,21 @@ int Model::load(const char* path, const b2_load_opts* o) {
 
     max_batch = o && o->max_batch > 0 ? o->max_batch : 1;
     max_ctx = o && o->max_ctx > 0 ? std::min(o->max_ctx, hp.n_ctx) : hp.n_ctx;
-    if (o && o->tp_size > 1) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor parallelism (tp_size=%d) is not built yet", o->tp_size);
+    if (tp_size > 1) {
+        if (hp.arch != 0) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor parallelism is built for the llama graph only");
+        if (hp.n_head % tp_size || hp.n_head_kv % tp_size || hp.n_ff % tp_size || (hp.n_ff / tp_size) % 32)
+            B2_FAIL(B2_ERR_UNSUPPORTED, "tp_size=%d does not divide %d heads / %d KV heads / n_ff %d into whole blocks", tp_size, hp.n_head, hp.n_head_kv, hp.n_ff);
+    }
+    n_head_l = hp.n_head / tp_size; n_head_kv_l = hp.n_head_kv / tp_size; n_ff_l = hp.n_ff / tp_size;
     const int flags = o ? o->flags : 0;
     use_pdl = !(flags & B2_LOAD_NO_PDL) && !getenv("B2_NO_PDL");
     use_graph = !(flags & B2_LOAD_NO_GRAPH) && !getenv("B2_NO_GRAPH");
     use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
     use_batch = !(flags & B2_LOAD_NO_BATCH) && !getenv("B2_NO_BATCH");
+    if (tp_size > 1) use_mega = use_batch = false;      // shards run the per-matrix kernels with an all-reduce after wo and down
 
-    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd, F = hp.n_ff, V = hp.n_vocab;
+    const int E = hp.n_embd, hd = hp.head_dim, nq_full = hp.n_head * hd, nkv_full = hp.n_head_kv * hd, F_full = hp.n_ff, V = hp.n_vocab;
+    const int nq = n_head_l * hd, nkv = n_head_kv_l * hd, F = n_ff_l;       // this shard's part
     if ((nq | nkv | F | V | E) & 1) B2_FAIL(B2_ERR_UNSUPPORTED, "odd matrix dimensions are not supported");
 
     // ---- plan: which file tensors feed which resident matrices ---------------------------------
@@ -202,10 +222,10 @@ int Model::load(const char* path, const b2_load_opts* o) {
         const std::string p = "blk." + std::to_string(l) + ".";
         LayerPlan& L = lp[l];
         if (hp.arch == 0) {
-            B2_TRY(need(f, p + "attn_q.weight", nq, E, &L.q));
-            B2_TRY(need(f, p + "attn_k.weight", nkv, E, &L.k));
-            B2_TRY(need(f, p + "attn_v.weight", nkv, E, &L.v));
-            B2_TRY(need(f, p + "ffn_gate.weight", F, E, &L.gate));
+            B2_TRY(need(f, p + "attn_q.weight", nq_full, E, &L.q));
+            B2_TRY(need(f, p + "attn_k.weight", nkv_full, E, &L.k));
+            B2_TRY(need(f, p + "attn_v.weight", nkv_full, E, &L.v));
+            B2_TRY(need(f, p + "ffn_gate.weight", F_full, E, &L.gate));
             arena_bytes += qmat_arena_bytes(L.q.t->type, nq, E) + qmat_arena_bytes(L.k.t->type, nkv, E) + qmat_arena_bytes(L.v.t->type, nkv, E);
             arena_bytes += qmat_arena_bytes(L.gate.t->type, 2 * (int64_t)F, E);
             max_raw = std::max({max_raw, L.q.t->bytes, L.k.t->bytes, L.v.t->bytes, L.gate.t->bytes});
@@ -214,9 +234,9 @@ int Model::load(const char* path, const b2_load_opts* o) {
             arena_bytes += qmat_arena_bytes(L.qkv.t->type, nq + 2 * nkv, E);
             max_raw = std::max(max_raw, L.qkv.t->bytes);
         }
-        B2_TRY(need(f, p + "attn_output.weight", E, nq, &L.o));
-        B2_TRY(need(f, p + "ffn_up.weight", F, E, &L.up));
-        B2_TRY(need(f, p + "ffn_down.weight", E, F, &L.down));
+        B2_TRY(need(f, p + "attn_output.weight", E, nq_full, &L.o));
+        B2_TRY(need(f, p + "ffn_up.weight", F_full, E, &L.up));
+        B2_TRY(need(f, p + "ffn_down.weight", E, F_full, &L.down));
         if (hp.arch == 0 && L.gate.t->type != L.up.t->type) B2_FAIL(B2_ERR_UNSUPPORTED, "layer %d: ffn_gate and ffn_up differ in type", l);
         if (hp.arch == 1) arena_bytes += qmat_arena_bytes(L.up.t->type, F, E);
         arena_bytes += qmat_arena_bytes(L.o.t->type, E, nq) + qmat_arena_bytes(L.down.t->type, E, F);
@@ -262,7 +282,7 @@ int Model::load(const char* path, const b2_load_opts* o) {
                 B2_TRY(qmat_alloc(arena, seg.W, parts[i]->t->type, rows, E));
                 int64_t r = 0;
                 for (int q = i; q < j; q++) {
-                    B2_TRY(upload_rows_headwise(parts[q]->t, prow[q] / hd, E, seg.W, r, 0));
+                    B2_TRY(upload_rows_headwise(parts[q]->t, prow[q] / hd, E, seg.W, r, (int64_t)tp_rank * prow[q]));
                     r += prow[q];
                 }
                 L.qkv.push_back(seg);
@@ -271,8 +291,8 @@ int Model::load(const char* path, const b2_load_opts* o) {
             }
             B2_TRY(upload_f32(f, p + "ffn_norm.weight", E, &L.ffn_norm, false));
             B2_TRY(qmat_alloc(arena, L.w_up, P.gate.t->type, 2 * (int64_t)F, E));      // rows interleaved (gate_i, up_i)
-            B2_TRY(upload_quant(P.gate.t, F, E, L.w_up, 0, 2, 0));
-            B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 1, 2, 0));
+            B2_TRY(upload_quant(P.gate.t, F, E, L.w_up, 0, 2, (int64_t)tp_rank * F));
+            B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 1, 2, (int64_t)tp_rank * F));
         } else {
             QkvSeg seg;
             seg.row0 = 0;
@@ -301,9 +321,14 @@ int Model::load(const char* path, const b2_load_opts* o) {
             B2_TRY(upload_f32(f, p + "attn_output.bias", E, &L.b_o, true));
         }
         B2_TRY(qmat_alloc(arena, L.w_o, P.o.t->type, E, nq));
-        B2_TRY(upload_quant(P.o.t, E, nq, L.w_o, 0, 1, 0));
         B2_TRY(qmat_alloc(arena, L.w_down, P.down.t->type, E, F));
-        B2_TRY(upload_quant(P.down.t, E, F, L.w_down, 0, 1, 0));
+        if (tp_size == 1) {
+            B2_TRY(upload_quant(P.o.t, E, nq, L.w_o, 0, 1, 0));
+            B2_TRY(upload_quant(P.down.t, E, F, L.w_down, 0, 1, 0));
+        } else {          // K slices: this shard's heads of the attention output, its rows of the FFN hidden vector
+            B2_TRY(upload_quant_kslice(P.o.t, E, nq_full, (int64_t)tp_rank * nq, nq, L.w_o));
+            B2_TRY(upload_quant_kslice(P.down.t, E, F_full, (int64_t)tp_rank * F, F, L.w_down));
+        }
         for (auto& s : L.qkv) step_weight_bytes += gemv_weight_bytes(s.W);
         step_weight_bytes += gemv_weight_bytes(L.w_o) + gemv_weight_bytes(L.w_up) + gemv_weight_bytes(L.w_down) + (size_t)2 * E * 4;
     }
@@ -357,12 +382,48 @@ int Model::load(const char* path, const b2_load_opts* o) {
         B2_CUDA(cudaMalloc(&rope_table, tab.size() * sizeof(float2)));
         B2_CUDA(cudaMemcpy(rope_table, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
     }
+    if (tp_size > 1) return tp_alloc();       // the pipelines are built by tp_connect once every shard is loaded
+    return finish_load();
+}
+
+int Model::finish_load() {
     for (Slot& s : slots) {
         build_ops(s);
         B2_TRY(setup_mega(s));
     }
     if (use_batch) B2_TRY(setup_batch());
     return B2_OK;
+}
+
+int Model::tp_alloc() {
+    const size_t part_bytes = (size_t)hp.n_embd * sizeof(double), total = 2 * part_bytes + 256 + 256;
+    B2_CUDA(cudaMalloc(&tp_mem, total));
+    B2_CUDA(cudaMemset(tp_mem, 0, total));
+    return B2_OK;
+}
+
+int Model::tp_connect(Model* const* shards) {
+    B2_CUDA(cudaSetDevice(device));
+    const size_t part_bytes = (size_t)hp.n_embd * sizeof(double);
+    tp = TpPeers();
+    tp.n = tp_size; tp.rank = tp_rank;
+    for (int d = 0; d < tp_size; d++) {
+        if (d != tp_rank) {
+            int can = 0;
+            B2_CUDA(cudaDeviceCanAccessPeer(&can, device, shards[d]->device));
+            if (!can) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor parallelism needs peer access between GPU %d and GPU %d", device, shards[d]->device);
+            const cudaError_t e = cudaDeviceEnablePeerAccess(shards[d]->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) B2_CUDA(e);
+            cudaGetLastError();
+        }
+        uint8_t* b = (uint8_t*)shards[d]->tp_mem;
+        tp.part[0][d] = (double*)b;
+        tp.part[1][d] = (double*)(b + part_bytes);
+        tp.flags[d] = (unsigned*)(b + 2 * part_bytes);
+    }
+    tp.epoch = (unsigned*)((uint8_t*)tp_mem + 2 * part_bytes + 256);
+    tp.ticket = tp.epoch + 1;
+    return finish_load();
 }
 
 // ---- sequences -------------------------------------------------------------------------------------
@@ -418,7 +479,7 @@ int Model::ensure_pages(Slot& s, int upto) {
 
 // ---- the layer pipeline of one sequence slot: 5 ops per layer (qkv may be split by tensor type) -----
 void Model::build_ops(Slot& s) {
-    const int hd = hp.head_dim, nq = hp.n_head * hd, nkv = hp.n_head_kv * hd;
+    const int hd = hp.head_dim, nq = n_head_l * hd, nkv = n_head_kv_l * hd;
     s.ops.clear();
     for (int l = 0; l < hp.n_layer; l++) {
         const LayerW& L = layers[l];
@@ -441,7 +502,7 @@ void Model::build_ops(Slot& s) {
             StepOp op; op.kind = 1; op.cls = 2;
             AttnArgs& a = op.a;
             a.q = s.q; a.out = s.att; a.k_base = kb; a.v_base = vb; a.page_table = s.d_page_table; a.pos = s.d_pos;
-            a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.head_dim = hd; a.page_tokens = PAGE_TOKENS; a.kv_dim = nkv;
+            a.n_head = n_head_l; a.n_head_kv = n_head_kv_l; a.head_dim = hd; a.page_tokens = PAGE_TOKENS; a.kv_dim = nkv;
             a.max_ctx = max_ctx;
             a.scale = hp.arch == 1 ? 1.0f : 1.0f / sqrtf((float)hd);
             s.ops.push_back(op);
@@ -452,6 +513,10 @@ void Model::build_ops(Slot& s) {
             o.g.W = L.w_o; o.g.pro = PRO_PLAIN; o.g.epi = EPI_RESIDUAL; o.g.x = s.att; o.g.y = s.x;
             u.g.W = L.w_up; u.g.pro = PRO_RMSNORM; u.g.epi = EPI_SILU_MUL; u.g.x = s.x; u.g.gain = L.ffn_norm; u.g.eps = hp.norm_eps; u.g.y = s.h;
             d.g.W = L.w_down; d.g.pro = PRO_PLAIN; d.g.epi = EPI_RESIDUAL; d.g.x = s.h; d.g.y = s.x;
+            if (tp_size > 1) {      // K-split projections: unrounded partial sums, then the all-reduce adds the residual
+                o.g.epi = EPI_PARTIAL; o.g.y64 = tp.part[0][tp_rank]; o.tp_buf = 0;
+                d.g.epi = EPI_PARTIAL; d.g.y64 = tp.part[1][tp_rank]; d.tp_buf = 1;
+            }
         } else {
             o.g.W = L.w_o; o.g.pro = PRO_PLAIN; o.g.epi = EPI_STORE; o.g.x = s.att; o.g.bias = L.b_o; o.g.y = s.att2;
             u.g.W = L.w_up; u.g.pro = PRO_LAYERNORM; u.g.epi = EPI_GELU; u.g.x = s.x; u.g.gain = L.attn_norm; u.g.nbias = L.attn_norm_b;
@@ -541,6 +606,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
             if (op.kind == 0) B2_TRY(gemv_launch(op.g, stream, pdl));
             else B2_TRY(attn_decode_launch(op.a, stream, pdl));
             nl++;
+            if (op.tp_buf >= 0) { B2_TRY(tp_allreduce_residual_launch(tp, op.tp_buf, s.x, hp.n_embd, stream)); nl++; }
             B2_TRY(mark(op.cls));
         }
     }
@@ -787,7 +853,7 @@ int Model::kv_read(int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_t
     B2_TRY(check_seq(seq));
     Slot& s = slots[seq];
     if (layer < 0 || layer >= hp.n_layer || n_tok < 0 || n_tok > s.len) B2_FAIL(B2_ERR_ARG, "kv_read: layer %d / n_tok %d out of range", layer, n_tok);
-    const size_t nkv = (size_t)hp.n_head_kv * hp.head_dim;
+    const size_t nkv = (size_t)n_head_kv_l * hp.head_dim;      // this shard's KV heads
     for (int t0 = 0; t0 < n_tok; t0 += PAGE_TOKENS) {
         const int cnt = std::min(PAGE_TOKENS, n_tok - t0);
         const size_t src = ((size_t)s.pages[t0 / PAGE_TOKENS] * PAGE_TOKENS) * nkv + layer_kv_elems * layer;

@@ -36,7 +36,7 @@ struct LayerW {
     float *b_qkv = nullptr, *b_o = nullptr, *b_up = nullptr, *b_down = nullptr;
 };
 
-struct StepOp { int kind = 0; int cls = 0; GemvArgs g; AttnArgs a; };     // kind 0 = GEMV, 1 = attention
+struct StepOp { int kind = 0; int cls = 0; GemvArgs g; AttnArgs a; int tp_buf = -1; };     // kind 0 = GEMV, 1 = attention; tp_buf >= 0: all-reduce follows
 
 struct Slot {
     bool used = false;
@@ -81,7 +81,12 @@ struct BatchCtx {
 struct StepProfile { std::vector<cudaEvent_t> ev; std::vector<int> cls; };
 
 struct Model {
-    HParams hp;
+    HParams hp;                       // the whole model's hyper-parameters
+    int tp_rank = 0, tp_size = 1;     // this shard of a tensor-parallel group (one shard per GPU)
+    int n_head_l = 0, n_head_kv_l = 0, n_ff_l = 0;     // heads / FFN rows held by this shard
+    TpPeers tp;                       // peer-mapped partial-sum buffers and flags (tp_size > 1)
+    void* tp_mem = nullptr;
+    int device = 0;
     bool neox = false, use_pdl = true, use_graph = true, use_mega = true, use_batch = true;
     int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
     float2* rope_table = nullptr;     // [max_ctx][n_rot/2]
@@ -104,7 +109,10 @@ struct Model {
     double last_ms = 0;
 
     ~Model();
-    int load(const char* path, const b2_load_opts* o);
+    int load(const char* path, const b2_load_opts* o, int tp_rank = 0, int tp_size = 1);
+    int tp_alloc();                                     // this shard's exchange buffers (before tp_connect)
+    int tp_connect(Model* const* shards);               // peer-map every shard's buffers, then build the step pipelines
+    int finish_load();
     int seq_new(int* out);
     int seq_free(int seq);
     int seq_truncate(int seq, int n_keep);
@@ -118,6 +126,7 @@ struct Model {
 
   private:
     int upload_quant(const GgufTensor* t, int64_t rows, int64_t k, const QMat& dst, int64_t dst_row0, int64_t dst_row_step, int64_t src_row0);
+    int upload_quant_kslice(const GgufTensor* t, int64_t rows, int64_t k_full, int64_t k0, int64_t kl, const QMat& dst);
     int upload_f32(const GgufFile& f, const std::string& name, int64_t n, float** out, bool optional);
     int upload_rows_headwise(const GgufTensor* t, int64_t n_heads, int64_t k, const QMat& dst, int64_t dst_row0, int64_t src_row0);
     void build_ops(Slot& s);

@@ -220,11 +220,8 @@ template <int NT>
 int gemm_launch_t(const GemmMaps& maps, const Q8Cols& x, int rows, int nbk, int B, const GemvArgs* colargs, const int* pos, const int* pt, int pt_stride, int grid,
                   cudaStream_t st) {
     auto kern = gemm_w4a8_kernel<NT>;
-    static bool configured = false;
-    if (!configured) {
-        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GB_SMEM));
-        configured = true;
-    }
+    static PerDeviceSmem configured;
+    if (configured.raise(GB_SMEM)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GB_SMEM));
     kern<<<grid, (GB_WARPS + 1) * 32, GB_SMEM, st>>>(maps, x, rows, nbk, B, colargs, pos, pt, pt_stride);
     B2_CUDA(cudaGetLastError());
     return B2_OK;

@@ -153,7 +153,12 @@ __global__ void __launch_bounds__((TYPE == T_Q4_K || TYPE == T_Q6_K) ? 288 : 544
             if (2 * lane < c.RPG && r < rows_here) {
                 double d0 = 0.0, d1 = 0.0;
                 for (int k = 0; k < c.S; k++) { d0 += redt[r * c.S + k]; d1 += redt[(r + 1) * c.S + k]; }
-                epilogue_pair(a, a.epi_row0 + row0 + r, (float)d0, (float)d1, best);
+                if (a.epi == EPI_PARTIAL) {          // tensor-parallel K slice: the f64 partial sums go to the all-reduce unrounded
+                    a.y64[a.epi_row0 + row0 + r] = d0;
+                    a.y64[a.epi_row0 + row0 + r + 1] = d1;
+                } else {
+                    epilogue_pair(a, a.epi_row0 + row0 + r, (float)d0, (float)d1, best);
+                }
             }
         }
     }
@@ -181,11 +186,8 @@ int sm_count() {
 template <int TYPE, int NB>
 int launch_t(const GemvArgs& a, const GemvCfg& c, int grid, int threads, size_t smem, cudaStream_t st, bool pdl) {
     auto kern = gemv_kernel<TYPE, NB>;
-    static size_t configured = 0;     // per instantiation
-    if (smem > configured) {
-        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static PerDeviceSmem configured;     // per instantiation
+    if (configured.raise(smem)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(threads);

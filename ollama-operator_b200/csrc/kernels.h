@@ -24,6 +24,7 @@ enum GemvEpi : int {
     EPI_LOGITS = 4,      // y[r] = v and a running arg-max into *argmax_key
     EPI_GELU = 5,        // y[r] = gelu(v)
     EPI_RESIDUAL2 = 6,   // y[r] = (v + y2[r]) + y[r]   (phi-2 parallel block: ffn + attn + x)
+    EPI_PARTIAL = 7,     // y64[r] = the f64 sum, unrounded (tensor-parallel K slice; per-matrix GEMV only)
 };
 
 struct KvDesc {                 // where the new token's K and V go (one layer, one sequence slot)
@@ -44,6 +45,7 @@ struct GemvArgs {
     const float* bias = nullptr;   // [rows] optional, added before the epilogue
     float* y = nullptr;
     const float* y2 = nullptr;
+    double* y64 = nullptr;         // EPI_PARTIAL
     int64_t epi_row0 = 0;          // added to the matrix row before the epilogue (split QKV matrices)
     // EPI_QKV_ROPE
     int n_q = 0, n_kv = 0, head_dim = 0, n_rot = 0, rope_neox = 0;
@@ -106,6 +108,19 @@ bool mega_supported(int type, int grp, int head_dim);
 int mega_plan_stage(MegaStage& st, int ncw);
 int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);
 int mega_launch(const MegaLaunch& L, cudaStream_t stream);
+
+// ---- tp.cu: tensor-parallel all-reduce over peer memory (one process, one engine shard per GPU) ------------
+constexpr int TP_MAX = 8;
+struct TpPeers {
+    int n = 1, rank = 0;
+    double* part[2][TP_MAX] = {};     // [buffer][device]: every shard's partial sums (peer-mapped pointers)
+    unsigned* flags[TP_MAX] = {};     // [device]: flags[d][r] = last epoch shard r published to device d
+    unsigned* epoch = nullptr;        // local: epochs completed so far
+    unsigned* ticket = nullptr;       // local: CTA exit counter of the reduce kernel
+};
+// x[i] += (float)(sum over shards of part[buf][d][i]), the same bits on every shard (fixed order, f64):
+// publishes this shard's epoch to all peers, waits for theirs, then reads their partial sums over NVLink.
+int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st);
 
 // ---- step.cu: per-step bookkeeping kernels ----------------------------------------------------
 struct SeqState {        // one per sequence slot, resident on the device

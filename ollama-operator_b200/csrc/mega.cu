@@ -379,11 +379,10 @@ int mega_plan_stage(MegaStage& st, int ncw) {
 template <int TYPE, int NB, int NCW, int GRP, int HD>
 static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSmem configured;
+    if (configured.raise(L.smem_bytes)) {
         B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
         B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
-        configured = true;
     }
     MegaSmem sm;
     sm.off_red = L.off_red; sm.off_xq = L.off_xq; sm.off_xd = L.off_xd; sm.off_xs = L.off_xs; sm.off_att = L.off_att; sm.off_ring = L.off_ring;

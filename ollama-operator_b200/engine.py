@@ -177,15 +177,16 @@ def attn_bench(n_ctx: int, n_head: int, n_head_kv: int, head_dim: int, cluster: 
 
 # ---- engine -------------------------------------------------------------------------------------------
 class Engine:
-    """One CUDA device bound through b2_init."""
+    """The CUDA device(s) bound through b2_init: one index, or a list for tensor parallelism."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device=0):
         self._h = C.c_void_p()
-        ids = (C.c_int * 1)(device)
-        _check(lib().b2_init(1, ids, C.byref(self._h)))
+        devs = [device] if isinstance(device, int) else list(device)
+        ids = (C.c_int * len(devs))(*devs)
+        _check(lib().b2_init(len(devs), ids, C.byref(self._h)))
 
-    def load(self, path: str, max_batch: int = 1, max_ctx: int = 0, flags: int = 0) -> "Model":
-        return Model(self, path, max_batch, max_ctx, flags)
+    def load(self, path: str, max_batch: int = 1, max_ctx: int = 0, flags: int = 0, tp_size: int = 1) -> "Model":
+        return Model(self, path, max_batch, max_ctx, flags, tp_size)
 
     def close(self):
         if self._h:
@@ -194,10 +195,10 @@ class Engine:
 
 
 class Model:
-    def __init__(self, eng: Engine, path: str, max_batch: int = 1, max_ctx: int = 0, flags: int = 0):
+    def __init__(self, eng: Engine, path: str, max_batch: int = 1, max_ctx: int = 0, flags: int = 0, tp_size: int = 1):
         self.eng = eng
         self._h = C.c_void_p()
-        opts = LoadOpts(max_batch, max_ctx, 1, flags)
+        opts = LoadOpts(max_batch, max_ctx, tp_size, flags)
         _check(lib().b2_model_load(eng._h, os.fsencode(path), C.byref(opts), C.byref(self._h)))
         self.info = ModelInfo()
         _check(lib().b2_model_get_info(self._h, C.byref(self.info)))

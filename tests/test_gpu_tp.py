@@ -1,0 +1,57 @@
+"""Tensor parallelism (one engine shard per GPU, all-reduce of the K-split projections over peer
+memory): the shards add their unrounded f64 partial sums in a fixed order and round once, so the
+results must be the bits of the single-GPU run -- logits, KV rows and greedy tokens."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+@pytest.mark.parametrize("preset,tp", [("tiny-llama", 2), ("tiny-gqa", 2), ("tiny-llama", 4)])
+def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp):
+    if _n_gpus() < tp:
+        pytest.skip(f"needs {tp} GPUs")
+    E = pkg.engine
+    path = pkg.synth.cached_model(preset, model_dir)
+    e1, en = E.Engine(0), E.Engine(list(range(tp)))
+    m1 = e1.load(path, max_batch=2, max_ctx=256)
+    mt = en.load(path, max_batch=2, max_ctx=256, tp_size=tp)
+    assert mt.info.n_head == m1.info.n_head and mt.info.step_weight_bytes >= m1.info.step_weight_bytes
+    toks = pkg.synth.prompt_tokens(21, m1.info.n_vocab, seed=5)
+    s1, st = m1.seq_new(), mt.seq_new()
+    l1, lt = m1.prefill(s1, toks), mt.prefill(st, toks)
+    assert np.array_equal(_bits(l1), _bits(lt)), np.abs(l1 - lt).max()
+    # against the oracle directly as well
+    om = oracle.OracleModel(path, faithful=2)
+    for t in toks:
+        want = om.eval(int(t))
+    assert np.array_equal(_bits(lt), _bits(want))
+    for layer in range(m1.info.n_layer):
+        k1, v1 = m1.kv_read(s1, layer, len(toks))
+        kt, vt = mt.kv_read(st, layer, len(toks))
+        assert np.array_equal(k1.view(np.uint16), kt.view(np.uint16)) and np.array_equal(v1.view(np.uint16), vt.view(np.uint16)), layer
+    assert np.array_equal(m1.decode_greedy(s1, 40), mt.decode_greedy(st, 40))
+    tok = 7
+    for _ in range(5):
+        n1, g1 = m1.decode([s1], [tok], want_logits=True)
+        nt, gt = mt.decode([st], [tok], want_logits=True)
+        assert np.array_equal(_bits(g1), _bits(gt)) and n1[0] == nt[0]
+        tok = int(n1[0])
+    # a second sequence on the same shards
+    s1b, stb = m1.seq_new(), mt.seq_new()
+    assert s1b == stb
+    more = pkg.synth.prompt_tokens(9, m1.info.n_vocab, seed=6)
+    assert np.array_equal(_bits(m1.prefill(s1b, more)), _bits(mt.prefill(stb, more)))
+    mt.close(); m1.close(); en.close(); e1.close()
