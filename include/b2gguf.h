@@ -48,7 +48,8 @@ typedef struct b2_model b2_model;   /* weights resident in HBM + KV cache + sequ
 typedef struct {
     int32_t max_batch;   /* sequence slots (0 -> 1) */
     int32_t max_ctx;     /* tokens per sequence (0 -> the model's context length) */
-    int32_t tp_size;     /* tensor-parallel degree; 1 in this round */
+    int32_t tp_size;     /* tensor-parallel degree (0/1 = one GPU); needs that many devices in b2_init with peer access;
+                            llama graph only; results are bit-identical to tp_size 1 */
     int32_t flags;       /* B2_LOAD_* */
 } b2_load_opts;
 enum { B2_LOAD_NO_PDL = 1,      /* do not use programmatic dependent launch */

@@ -202,6 +202,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     use_graph = !(flags & B2_LOAD_NO_GRAPH) && !getenv("B2_NO_GRAPH");
     use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
     use_batch = !(flags & B2_LOAD_NO_BATCH) && !getenv("B2_NO_BATCH");
+    tp_skip_reduce = getenv("B2_TP_SKIP_REDUCE") != nullptr;      // timing experiment only: results are wrong
     if (tp_size > 1) use_mega = use_batch = false;      // shards run the per-matrix kernels with an all-reduce after wo and down
 
     const int E = hp.n_embd, hd = hp.head_dim, nq_full = hp.n_head * hd, nkv_full = hp.n_head_kv * hd, F_full = hp.n_ff, V = hp.n_vocab;
@@ -606,7 +607,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
             if (op.kind == 0) B2_TRY(gemv_launch(op.g, stream, pdl));
             else B2_TRY(attn_decode_launch(op.a, stream, pdl));
             nl++;
-            if (op.tp_buf >= 0) { B2_TRY(tp_allreduce_residual_launch(tp, op.tp_buf, s.x, hp.n_embd, stream)); nl++; }
+            if (op.tp_buf >= 0 && !tp_skip_reduce) { B2_TRY(tp_allreduce_residual_launch(tp, op.tp_buf, s.x, hp.n_embd, stream, pdl)); nl++; }
             B2_TRY(mark(op.cls));
         }
     }

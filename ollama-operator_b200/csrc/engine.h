@@ -87,6 +87,7 @@ struct Model {
     TpPeers tp;                       // peer-mapped partial-sum buffers and flags (tp_size > 1)
     void* tp_mem = nullptr;
     int device = 0;
+    bool tp_skip_reduce = false;
     bool neox = false, use_pdl = true, use_graph = true, use_mega = true, use_batch = true;
     int max_batch = 1, max_ctx = 0, pages_per_seq = 0, n_pages = 0, out_cap = 0;
     float2* rope_table = nullptr;     // [max_ctx][n_rot/2]

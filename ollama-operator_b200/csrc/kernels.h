@@ -120,7 +120,7 @@ struct TpPeers {
 };
 // x[i] += (float)(sum over shards of part[buf][d][i]), the same bits on every shard (fixed order, f64):
 // publishes this shard's epoch to all peers, waits for theirs, then reads their partial sums over NVLink.
-int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st);
+int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st, bool pdl);
 
 // ---- step.cu: per-step bookkeeping kernels ----------------------------------------------------
 struct SeqState {        // one per sequence slot, resident on the device

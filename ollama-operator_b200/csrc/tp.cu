@@ -34,11 +34,13 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 }
 __device__ __forceinline__ double2 ld_relaxed_sys_f64x2(const double* p) {
     double2 v;
-    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
     return v;
 }
 
 __global__ void __launch_bounds__(256) tp_allreduce_residual_kernel(const TpPeers p, const int buf, float* __restrict__ x, const int n) {
+    pdl_trigger();       // the next GEMV may start streaming its weights; it waits for this kernel before touching x
+    pdl_wait();          // the GEMV that wrote our partial sums has completed and flushed
     const unsigned e = *reinterpret_cast<volatile unsigned*>(p.epoch) + 1;     // the same value in every CTA: only the last CTA to leave bumps it
     if (blockIdx.x == 0 && threadIdx.x < p.n && (int)threadIdx.x != p.rank) {
         // the GEMV that wrote our partial sums finished before this kernel started (stream order)
@@ -52,12 +54,15 @@ __global__ void __launch_bounds__(256) tp_allreduce_residual_kernel(const TpPeer
     }
     __syncthreads();
     for (int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x); i < n; i += 2 * gridDim.x * blockDim.x) {
+        // all peers' values in flight at once (one NVLink round trip, not one per peer), then the fixed-order sum
+        double2 v[TP_MAX];
+#pragma unroll
+        for (int d = 0; d < TP_MAX; d++)
+            if (d < p.n) v[d] = ld_relaxed_sys_f64x2(p.part[buf][d] + i);
         double s0 = 0.0, s1 = 0.0;
-        for (int d = 0; d < p.n; d++) {
-            const double2 v = ld_relaxed_sys_f64x2(p.part[buf][d] + i);
-            s0 += v.x;
-            s1 += v.y;
-        }
+#pragma unroll
+        for (int d = 0; d < TP_MAX; d++)
+            if (d < p.n) { s0 += v[d].x; s1 += v[d].y; }
         float2 r = *reinterpret_cast<float2*>(x + i);
         r.x = __fadd_rn(r.x, (float)s0);
         r.y = __fadd_rn(r.y, (float)s1);
@@ -76,11 +81,19 @@ __global__ void __launch_bounds__(256) tp_allreduce_residual_kernel(const TpPeer
 
 }  // namespace
 
-int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st) {
+int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st, bool pdl) {
     if (p.n < 2 || p.n > TP_MAX || (n & 1) || buf < 0 || buf > 1) B2_FAIL(B2_ERR_ARG, "tp all-reduce: bad arguments");
-    const int grid = std::max(1, std::min(16, n / 512));
-    tp_allreduce_residual_kernel<<<grid, 256, 0, st>>>(p, buf, x, n);
-    B2_CUDA(cudaGetLastError());
+    const int grid = std::max(1, std::min(32, n / 512));     // one pair of elements per thread
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, tp_allreduce_residual_kernel, p, buf, x, n));
     return B2_OK;
 }
 
