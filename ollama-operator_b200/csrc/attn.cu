@@ -55,6 +55,8 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_batch_kernel(const At
         mbar_fence_init();
     }
     cluster_sync_all();
+    pdl_trigger();
+    pdl_wait();                  // q and this step's K/V rows come from the preceding kernel
     const AttnArgs a = args[blockIdx.z];
     uint32_t xphase = 0;
     attn_kv_head<GRP, HD, ATT_THREADS>(a, c, blockIdx.y, smem_raw, threadIdx.x, &xbar, xphase, 1);
@@ -70,11 +72,13 @@ int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg
     cfg.blockDim = dim3(ATT_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = c.cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     B2_CUDA(cudaLaunchKernelEx(&cfg, kern, d_args, c));
     return B2_OK;
 }

@@ -44,6 +44,8 @@ __global__ void __launch_bounds__(256) quant_cols_kernel(GemvArgs a, int64_t x_s
     __shared__ double dscratch[32];
     const int c = blockIdx.x, tid = threadIdx.x;
     a.x += (size_t)c * x_stride;
+    pdl_trigger();       // the batched kernel that consumes these columns may start streaming its weights
+    pdl_wait();          // the activations come from the preceding kernel, which may also still be reading the buffer we overwrite
     const ProStats st = prologue_stats(a, dscratch, tid, 256);
     prologue_q8_0_each(a, st, tid, 256, [=](int blk, int o, uint32_t w, float d, int s8) {
         const int kc = blk / GEMM_KC, bl = blk % GEMM_KC;
@@ -72,8 +74,16 @@ int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pr
     if (K % 32 || K > out.k_cap) B2_FAIL(B2_ERR_ARG, "quant_cols: K=%lld", (long long)K);
     GemvArgs a;
     a.W.k = K; a.pro = pro; a.x = x; a.gain = gain; a.nbias = nbias; a.eps = eps;
-    quant_cols_kernel<<<B, 256, 0, st>>>(a, x_stride, out);
-    B2_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(B);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, quant_cols_kernel, a, x_stride, out));
     return B2_OK;
 }
 

@@ -69,11 +69,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
         "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
         : "memory");
 }
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-    uint64_t p;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
 __device__ __forceinline__ float half_of(uint32_t packed, int hi) {
     return __half2float(__ushort_as_half((unsigned short)(hi ? packed >> 16 : packed & 0xFFFFu)));
 }
@@ -103,33 +98,55 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
     }
     __syncthreads();
 
+    pdl_trigger();
     if (warp == GB_WARPS) {
         // ===== producer warp: every lane issues (at most) one TMA operation per stage =====
+        // The weights do not depend on the preceding kernel: their boxes for the first stages are issued
+        // before griddepcontrol.wait, the activation chunks (written by the preceding kernel) after it.
         const uint64_t pol_w = l2_policy_evict_first(), pol_x = l2_policy_evict_last();
-        uint32_t it = 0;
-        for (int grp = 0; grp < n_grp; grp++) {
-            const int gt0 = t0 + grp * per, n_rt = min(per, t1 - gt0);
-            for (int kc = 0; kc < n_kc; kc++, it++) {
-                const uint32_t s = it % GB_NS;
-                if (lane == 0) {
-                    if (it >= (uint32_t)GB_NS) mbar_wait(&empty[s], ((it / GB_NS) - 1) & 1);
-                    mbar_expect_tx(&full[s], (uint32_t)n_rt * (2 * GB_QBOX + GB_DBOX) + BP * GEMM_XCOL + 2 * GEMM_KC * BATCH_MAX * 4);
-                }
-                __syncwarp();
-                uint8_t* sb = ring + (size_t)s * GB_STAGE;
-                if (lane < 2 * n_rt) {
-                    const int rt = lane >> 1, sub = lane & 1;
-                    tma_load_2d(sb + (rt * 2 + sub) * GB_QBOX, &maps.q, (kc * GEMM_KC + sub * 8) * 16, (gt0 + rt) * 16, &full[s], pol_w);
-                } else if (lane >= 2 * GB_RTMAX && lane - 2 * GB_RTMAX < n_rt) {
-                    const int rt = lane - 2 * GB_RTMAX;
-                    tma_load_2d(sb + GB_OFF_D + rt * GB_DBOX, &maps.d, kc * GEMM_KC * 2, (gt0 + rt) * 16, &full[s], pol_w);
-                } else if (lane == 30) {
-                    bulk_g2s(sb + GB_OFF_XQ, xin.q + (size_t)kc * BATCH_MAX * GEMM_XCOL, BP * GEMM_XCOL, &full[s], pol_x);
-                } else if (lane == 31) {
-                    bulk_g2s(sb + GB_OFF_XD, xin.d + (size_t)kc * GEMM_KC * BATCH_MAX, GEMM_KC * BATCH_MAX * 4, &full[s], pol_x);
-                    bulk_g2s(sb + GB_OFF_XS, xin.s8 + (size_t)kc * GEMM_KC * BATCH_MAX, GEMM_KC * BATCH_MAX * 4, &full[s], pol_x);
-                }
+        const uint32_t n_it = (uint32_t)n_grp * (uint32_t)n_kc;
+        auto stage_of = [&](uint32_t it, int& gt0, int& n_rt, int& kc) {
+            const int grp = (int)(it / (uint32_t)n_kc);
+            kc = (int)(it % (uint32_t)n_kc);
+            gt0 = t0 + grp * per;
+            n_rt = min(per, t1 - gt0);
+        };
+        auto issue_w = [&](uint32_t it) {
+            int gt0, n_rt, kc;
+            stage_of(it, gt0, n_rt, kc);
+            const uint32_t s = it % GB_NS;
+            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)n_rt * (2 * GB_QBOX + GB_DBOX) + BP * GEMM_XCOL + 2 * GEMM_KC * BATCH_MAX * 4);
+            __syncwarp();
+            uint8_t* sb = ring + (size_t)s * GB_STAGE;
+            if (lane < 2 * n_rt) {
+                const int rt = lane >> 1, sub = lane & 1;
+                tma_load_2d(sb + (rt * 2 + sub) * GB_QBOX, &maps.q, (kc * GEMM_KC + sub * 8) * 16, (gt0 + rt) * 16, &full[s], pol_w);
+            } else if (lane >= 2 * GB_RTMAX && lane - 2 * GB_RTMAX < n_rt) {
+                const int rt = lane - 2 * GB_RTMAX;
+                tma_load_2d(sb + GB_OFF_D + rt * GB_DBOX, &maps.d, kc * GEMM_KC * 2, (gt0 + rt) * 16, &full[s], pol_w);
             }
+        };
+        auto issue_x = [&](uint32_t it) {
+            const int kc = (int)(it % (uint32_t)n_kc);
+            const uint32_t s = it % GB_NS;
+            uint8_t* sb = ring + (size_t)s * GB_STAGE;
+            if (lane == 30) {
+                bulk_g2s(sb + GB_OFF_XQ, xin.q + (size_t)kc * BATCH_MAX * GEMM_XCOL, BP * GEMM_XCOL, &full[s], pol_x);
+            } else if (lane == 31) {
+                bulk_g2s(sb + GB_OFF_XD, xin.d + (size_t)kc * GEMM_KC * BATCH_MAX, GEMM_KC * BATCH_MAX * 4, &full[s], pol_x);
+                bulk_g2s(sb + GB_OFF_XS, xin.s8 + (size_t)kc * GEMM_KC * BATCH_MAX, GEMM_KC * BATCH_MAX * 4, &full[s], pol_x);
+            }
+        };
+        const uint32_t n_pre = min(n_it, (uint32_t)GB_NS);
+        for (uint32_t it = 0; it < n_pre; it++) issue_w(it);
+        pdl_wait();
+        for (uint32_t it = 0; it < n_pre; it++) issue_x(it);
+        for (uint32_t it = n_pre; it < n_it; it++) {
+            const uint32_t s = it % GB_NS;
+            if (lane == 0) mbar_wait(&empty[s], ((it / GB_NS) - 1) & 1);
+            __syncwarp();
+            issue_w(it);
+            issue_x(it);
         }
         return;
     }
@@ -222,8 +239,17 @@ int gemm_launch_t(const GemmMaps& maps, const Q8Cols& x, int rows, int nbk, int 
     auto kern = gemm_w4a8_kernel<NT>;
     static PerDeviceSmem configured;
     if (configured.raise(GB_SMEM)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GB_SMEM));
-    kern<<<grid, (GB_WARPS + 1) * 32, GB_SMEM, st>>>(maps, x, rows, nbk, B, colargs, pos, pt, pt_stride);
-    B2_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3((GB_WARPS + 1) * 32);
+    cfg.dynamicSmemBytes = GB_SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, maps, x, rows, nbk, B, colargs, pos, pt, pt_stride));
     return B2_OK;
 }
 

@@ -294,9 +294,17 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 
         const int64_t pairs = a.W.rows >> 1;
         const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
+        // the stage descriptor lives in global memory and the waits below are compiler barriers: keep what
+        // the row loop needs in registers
+        uint32_t wstride[NP];
+#pragma unroll
+        for (int p = 0; p < NP; p++) wstride[p] = (uint32_t)a.W.stride[p];
+        unsigned long long c_wait = 0, c_dot = 0, c_red = 0, c0 = 0, c1 = 0, c2 = 0;
         for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
             const uint32_t s = it % sm.ns;
+            if (tr) c0 = (unsigned long long)clock64();
             if (!(sm.debug & 2)) mbar_wait(&full[s], (it / sm.ns) & 1);
+            if (tr) { c1 = (unsigned long long)clock64(); c_wait += c1 - c0; }
             const int rows_here = (int)min((int64_t)RT, r_end - row0);
             const uint8_t* sp = ring + (size_t)s * sm.stage_bytes;
             if (working && !(sm.debug & 1)) {
@@ -307,16 +315,18 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     const uint8_t* pb = sp;
 #pragma unroll
                     for (int p = 0; p < NP; p++) {
-                        rp0.p[p] = pb + (size_t)r * a.W.stride[p];
-                        rp1.p[p] = rp0.p[p] + a.W.stride[p];
-                        pb += (size_t)RT * a.W.stride[p];
+                        rp0.p[p] = pb + (uint32_t)r * wstride[p];
+                        rp1.p[p] = rp0.p[p] + wstride[p];
+                        pb += (uint32_t)RT * wstride[p];
                     }
+                    if (tr) c1 = (unsigned long long)clock64();
                     double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
                     for (int j = 0; j < NB; j++) {
                         acc0 += (double)unit_dot(xr[j], rp0, unit[j], nunits);
                         acc1 += (double)unit_dot(xr[j], rp1, unit[j], nunits);
                     }
+                    if (tr) { c2 = (unsigned long long)clock64(); c_dot += c2 - c1; }
                     const bool upper = (lane & 16) != 0;
                     double keep = upper ? acc1 : acc0;
                     const double give = upper ? acc0 : acc1;
@@ -324,6 +334,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 #pragma unroll
                     for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
                     if ((lane & 15) == 0) ysum[(size_t)(row0 - r_begin + r + (upper ? 1 : 0)) * Sw + ch] = keep;
+                    if (tr) c_red += (unsigned long long)clock64() - c2;
                 }
             }
             __syncwarp();
@@ -341,7 +352,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt);
             }
         }
-        if (tr) tr[3] = global_ns();
+        if (tr) { tr[3] = global_ns(); tr[11] = (c_wait << 42) | ((c_dot & 0x1FFFFF) << 21) | (c_red & 0x1FFFFF); }     // warp 0: cycles waiting for tiles / in row dots / reducing
     }
 }
 
