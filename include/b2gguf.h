@@ -94,6 +94,11 @@ int b2_seq_free(b2_model* m, int seq);
 int b2_seq_len(const b2_model* m, int seq);            /* tokens in the KV cache, or < 0 */
 int b2_seq_truncate(b2_model* m, int seq, int n_keep); /* drop cached tokens beyond n_keep */
 
+/* Tooling hook: declare the first n_tokens cache rows of the sequence valid without evaluating a prompt
+ * (their K/V are whatever the cache holds: zeros after load).  Lets a benchmark reach a long context
+ * without paying for the prefill; not for serving. */
+int b2_seq_assume(b2_model* m, int seq, int n_tokens);
+
 /* llama_decode over a prompt (upstream "prefill"): appends toks[0..n) to the sequence.
  * logits (n_vocab floats, may be NULL) receives the logits after the last token. */
 int b2_prefill(b2_model* m, int seq, const int32_t* toks, int n, float* logits);

@@ -187,6 +187,7 @@ int b2_seq_len(const b2_model* m, int seq) {
     return m->m.slots[seq].len;
 }
 int b2_seq_truncate(b2_model* m, int seq, int n_keep) { return tp_call(m, [&](Model& s, int) { return s.seq_truncate(seq, n_keep); }); }
+int b2_seq_assume(b2_model* m, int seq, int n_tokens) { return tp_call(m, [&](Model& s, int) { return s.seq_assume(seq, n_tokens); }); }
 int b2_prefill(b2_model* m, int seq, const int32_t* toks, int n, float* logits) {
     return tp_call(m, [&](Model& s, int r) { return s.prefill(seq, toks, n, r == 0 ? logits : nullptr); });
 }

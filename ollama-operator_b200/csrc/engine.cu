@@ -203,7 +203,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
     use_batch = !(flags & B2_LOAD_NO_BATCH) && !getenv("B2_NO_BATCH");
     tp_skip_reduce = getenv("B2_TP_SKIP_REDUCE") != nullptr;      // timing experiment only: results are wrong
-    if (tp_size > 1) use_mega = use_batch = false;      // shards run the per-matrix kernels with an all-reduce after wo and down
+    if (tp_size > 1) use_batch = false;      // prompts are walked token by token under tensor parallelism
 
     const int E = hp.n_embd, hd = hp.head_dim, nq_full = hp.n_head * hd, nkv_full = hp.n_head_kv * hd, F_full = hp.n_ff, V = hp.n_vocab;
     const int nq = n_head_l * hd, nkv = n_head_kv_l * hd, F = n_ff_l;       // this shard's part
@@ -461,6 +461,17 @@ int Model::seq_truncate(int seq, int n_keep) {
     while (s.pages.size() > keep_pages) { free_pages.push_back(s.pages.back()); s.pages.pop_back(); }
     return B2_OK;
 }
+// Tooling: declare cache rows [0, n) valid without evaluating a prompt (K/V are whatever the pages hold,
+// zeros after load) -- lets a benchmark reach a long context without paying for the prefill.
+int Model::seq_assume(int seq, int n) {
+    B2_TRY(check_seq(seq));
+    Slot& s = slots[seq];
+    if (n < s.len) B2_FAIL(B2_ERR_ARG, "seq_assume: %d is shorter than the sequence (%d)", n, s.len);
+    B2_TRY(ensure_pages(s, n));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    s.len = n;
+    return B2_OK;
+}
 // make sure pages exist for positions [0, upto) and the device page table matches
 int Model::ensure_pages(Slot& s, int upto) {
     if (upto > max_ctx) B2_FAIL(B2_ERR_NOMEM, "sequence would grow to %d tokens, max_ctx is %d", upto, max_ctx);
@@ -540,28 +551,43 @@ int Model::setup_mega(Slot& s) {
         }
     const int grp = hp.n_head / hp.n_head_kv;
     if (!mega_supported(type, grp, hp.head_dim)) return B2_OK;
-    std::vector<MegaStage> st(s.ops.size());
+    std::vector<MegaStage> st;
     int64_t k_max = 0;
     size_t tile_max = 0;
     int rt_s_max = 0;
     MegaLaunch& L = s.mega;
     L = MegaLaunch();
     L.type = type; L.grp = grp; L.head_dim = hp.head_dim; L.cluster = 4;
+    L.tp = tp;
     if (const char* v = getenv("B2_MEGA_CLUSTER")) L.cluster = atoi(v);
+    {   // kernel variant: 4 or 5 activation units per lane (K = 5120 needs 5 to keep one warp per row)
+        double c4 = 0, c5 = 0;
+        for (const StepOp& op : s.ops)
+            if (op.kind == 0) { c4 += mega_plan_cost(op.g.W, 4); c5 += mega_plan_cost(op.g.W, 5); }
+        L.nb = c5 < 0.9 * c4 ? 5 : 4;
+        if (const char* v = getenv("B2_MEGA_NB")) L.nb = atoi(v) == 5 ? 5 : 4;
+    }
     for (size_t i = 0; i < s.ops.size(); i++) {
-        st[i].kind = s.ops[i].kind;
+        MegaStage m;
+        m.kind = s.ops[i].kind;
         if (s.ops[i].kind == 0) {
-            st[i].g = s.ops[i].g;
-            if (mega_plan_stage(st[i], MEGA_NCW) != B2_OK) return B2_OK;
-            const QMat& W = st[i].g.W;
+            m.g = s.ops[i].g;
+            if (mega_plan_stage(m, MEGA_NCW, L.nb) != B2_OK) return B2_OK;
+            const QMat& W = m.g.W;
             size_t rb = 0;
             for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
             k_max = std::max(k_max, W.k);
-            tile_max = std::max(tile_max, rb * st[i].RT);
+            tile_max = std::max(tile_max, rb * m.RT);
             // per-CTA row-sum buffer: (rows of the CTA + slack) x S doubles; sized for the smallest grid we might get
-            rt_s_max = std::max(rt_s_max, (int)((W.rows / 64 + 4) * st[i].S));
+            rt_s_max = std::max(rt_s_max, (int)((W.rows / 64 + 4) * m.S));
         } else {
-            st[i].at = s.ops[i].a;
+            m.at = s.ops[i].a;
+        }
+        st.push_back(m);
+        if (s.ops[i].tp_buf >= 0) {          // K-split projection: the exchange with the other shards follows as a stage of its own
+            MegaStage x;
+            x.kind = 2; x.tp_buf = s.ops[i].tp_buf; x.tp_n = hp.n_embd; x.tp_x = s.x;
+            st.push_back(x);
         }
     }
     if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) {

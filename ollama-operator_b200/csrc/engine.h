@@ -117,6 +117,7 @@ struct Model {
     int seq_new(int* out);
     int seq_free(int seq);
     int seq_truncate(int seq, int n_keep);
+    int seq_assume(int seq, int n);
     int check_seq(int seq) const;
     int prefill(int seq, const int32_t* toks, int n, float* logits);
     int decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* next_tok, float* logits);

@@ -76,39 +76,6 @@ struct AttnArgs {
 };
 int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster = 0);
 
-// ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
-constexpr int MEGA_NCW = 15;      // consumer warps per CTA
-struct MegaStage {                // one stage of the layer pipeline, resident in device memory
-    int kind = 0;                 // 0 = GEMV, 1 = attention
-    GemvArgs g;
-    int S = 1;                    // warps along K per row
-    int P = 2;                    // warps sharing a row pair (each takes every P-th row)
-    int G = 1;                    // row groups per CTA (G * S * P <= MEGA_NCW)
-    int RPG = 2, RT = 2;          // rows per group per tile, rows per tile
-    int nunits = 0, nbeff = 4;    // units per row, units per lane actually used
-    AttnArgs at;
-    int att_max_local = 0;
-};
-struct MegaLaunch {
-    const MegaStage* stages = nullptr;   // device array
-    int s_begin = 0, s_end = 0;
-    unsigned* grid_count = nullptr;      // zeroed before every launch
-    unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
-    const int* pos = nullptr;            // device scalar: position of the token being decoded
-    const int* page_table = nullptr;     // this slot's page table
-    int n_pages = 0;
-    int type = 0, grp = 1, head_dim = 0, cluster = 4, grid = 0;
-    uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
-    int ns = 0, att_max_local = 0;
-    uint32_t pf_bytes = 0;               // L2 prefetch run-ahead per CTA, bytes (0 = off)
-    int debug = 0;                       // tuning experiments (see mega.cu), results are wrong when set
-    size_t smem_bytes = 0;
-};
-bool mega_supported(int type, int grp, int head_dim);
-int mega_plan_stage(MegaStage& st, int ncw);
-int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);
-int mega_launch(const MegaLaunch& L, cudaStream_t stream);
-
 // ---- tp.cu: tensor-parallel all-reduce over peer memory (one process, one engine shard per GPU) ------------
 constexpr int TP_MAX = 8;
 struct TpPeers {
@@ -121,6 +88,44 @@ struct TpPeers {
 // x[i] += (float)(sum over shards of part[buf][d][i]), the same bits on every shard (fixed order, f64):
 // publishes this shard's epoch to all peers, waits for theirs, then reads their partial sums over NVLink.
 int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st, bool pdl);
+
+// ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
+constexpr int MEGA_NCW = 15;      // consumer warps per CTA
+struct MegaStage {                // one stage of the layer pipeline, resident in device memory
+    int kind = 0;                 // 0 = GEMV, 1 = attention, 2 = tensor-parallel exchange (all-reduce + residual)
+    GemvArgs g;
+    int S = 1;                    // warps along K per row
+    int P = 2;                    // warps sharing a row pair (each takes every P-th row)
+    int G = 1;                    // row groups per CTA (G * S * P <= MEGA_NCW)
+    int RPG = 2, RT = 2;          // rows per group per tile, rows per tile
+    int nunits = 0, nbeff = 4;    // units per row, units per lane actually used
+    AttnArgs at;
+    int att_max_local = 0;
+    int tp_buf = 0, tp_n = 0;     // kind 2: which partial-sum buffer, vector length
+    float* tp_x = nullptr;        //         the residual stream the sum is added to
+};
+struct MegaLaunch {
+    const MegaStage* stages = nullptr;   // device array
+    int s_begin = 0, s_end = 0;
+    unsigned* grid_count = nullptr;      // zeroed before every launch
+    unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
+    const int* pos = nullptr;            // device scalar: position of the token being decoded
+    const int* page_table = nullptr;     // this slot's page table
+    int n_pages = 0;
+    int type = 0, grp = 1, head_dim = 0, cluster = 4, grid = 0;
+    int nb = 4;                          // units of the activation vector a lane keeps in registers (kernel variant)
+    uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
+    int ns = 0, att_max_local = 0;
+    uint32_t pf_bytes = 0;               // L2 prefetch run-ahead per CTA, bytes (0 = off)
+    int debug = 0;                       // tuning experiments (see mega.cu), results are wrong when set
+    size_t smem_bytes = 0;
+    TpPeers tp;                          // peers of the exchange stages (tp.n == 1: none)
+};
+bool mega_supported(int type, int grp, int head_dim);
+int mega_plan_stage(MegaStage& st, int ncw, int nb_max);
+double mega_plan_cost(const QMat& W, int nb_max);      // estimated consumer cost of a matrix with at most nb_max units per lane
+int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);
+int mega_launch(const MegaLaunch& L, cudaStream_t stream);
 
 // ---- step.cu: per-step bookkeeping kernels ----------------------------------------------------
 struct SeqState {        // one per sequence slot, resident on the device

@@ -65,9 +65,42 @@ __device__ __forceinline__ void grid_barrier(unsigned* count, unsigned& epoch, i
     named_bar_sync(1, ntc);
 }
 
-template <int TYPE, int NB, int NCW, int GRP, int HD>
+// Tensor-parallel exchange, after the grid barrier that completed this GPU's partial sums: publish the
+// epoch to the peers, wait for theirs, then every CTA reduces its slice of the vector (tp.cu has the protocol).
+// Kept out of line: its registers (one value per peer in flight) must not weigh on the GEMV stages.
+__device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf, float* x, int n, int tid, int ntc) {
+    if (tid < tp.n && tid != tp.rank) {
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(tp.flags[tid] + tp.rank), "r"(e) : "memory");
+        }
+        const unsigned* f = tp.flags[tp.rank] + tid;
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        } while ((int)(v - e) < 0);
+    }
+    named_bar_sync(1, ntc);
+    for (int i = 2 * (blockIdx.x * ntc + tid); i < n; i += 2 * gridDim.x * ntc) {
+        double2 v[TP_MAX];
+#pragma unroll
+        for (int d = 0; d < TP_MAX; d++)
+            if (d < tp.n) asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v[d].x), "=d"(v[d].y) : "l"(tp.part[buf][d] + i));
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int d = 0; d < TP_MAX; d++)
+            if (d < tp.n) { s0 += v[d].x; s1 += v[d].y; }
+        float2 r = *reinterpret_cast<float2*>(x + i);
+        r.x = __fadd_rn(r.x, (float)s0);
+        r.y = __fadd_rn(r.y, (float)s1);
+        *reinterpret_cast<float2*>(x + i) = r;
+    }
+}
+
+template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
-                                                                   const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages) {
+                                                                   const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages,
+                                                                   const __grid_constant__ TpPeers tp) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MEGA_NS_MAX;
@@ -165,6 +198,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     const int pos_now = s_pos;        // written before the __syncthreads above
     uint32_t it = 0, xphase = 0;
     unsigned epoch = 0;
+    unsigned tp_epoch = TP ? *reinterpret_cast<volatile unsigned*>(tp.epoch) : 0u;      // exchanges completed before this launch
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
     constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
     for (int st = s_begin; st < s_end; st++) {
@@ -173,6 +207,16 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         unsigned long long* tr = trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 12 : nullptr;
         if (tr) tr[0] = global_ns();
 
+        if (TP && S.kind == 2) {
+            // ---- tensor-parallel exchange: x += (float)(sum over the GPUs of the K-split partial sums) ----
+            // (tp.cu describes the protocol; here the publishing side is "all CTAs passed the grid barrier")
+            grid_barrier(grid_count, epoch, tid, ntc);              // this GPU's partial sums are complete
+            if (tr) tr[1] = global_ns();
+            tp_epoch++;
+            tp_exchange(tp, tp_epoch, S.tp_buf, S.tp_x, S.tp_n, tid, ntc);
+            if (tr) tr[2] = tr[3] = global_ns();
+            continue;
+        }
         if (S.kind != 0) {
             if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);
             if (tr) tr[1] = global_ns();
@@ -299,12 +343,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         uint32_t wstride[NP];
 #pragma unroll
         for (int p = 0; p < NP; p++) wstride[p] = (uint32_t)a.W.stride[p];
-        unsigned long long c_wait = 0, c_dot = 0, c_red = 0, c0 = 0, c1 = 0, c2 = 0;
         for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
             const uint32_t s = it % sm.ns;
-            if (tr) c0 = (unsigned long long)clock64();
             if (!(sm.debug & 2)) mbar_wait(&full[s], (it / sm.ns) & 1);
-            if (tr) { c1 = (unsigned long long)clock64(); c_wait += c1 - c0; }
             const int rows_here = (int)min((int64_t)RT, r_end - row0);
             const uint8_t* sp = ring + (size_t)s * sm.stage_bytes;
             if (working && !(sm.debug & 1)) {
@@ -319,14 +360,13 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                         rp1.p[p] = rp0.p[p] + wstride[p];
                         pb += (uint32_t)RT * wstride[p];
                     }
-                    if (tr) c1 = (unsigned long long)clock64();
+
                     double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
                     for (int j = 0; j < NB; j++) {
                         acc0 += (double)unit_dot(xr[j], rp0, unit[j], nunits);
                         acc1 += (double)unit_dot(xr[j], rp1, unit[j], nunits);
                     }
-                    if (tr) { c2 = (unsigned long long)clock64(); c_dot += c2 - c1; }
                     const bool upper = (lane & 16) != 0;
                     double keep = upper ? acc1 : acc0;
                     const double give = upper ? acc0 : acc1;
@@ -334,7 +374,6 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 #pragma unroll
                     for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
                     if ((lane & 15) == 0) ysum[(size_t)(row0 - r_begin + r + (upper ? 1 : 0)) * Sw + ch] = keep;
-                    if (tr) c_red += (unsigned long long)clock64() - c2;
                 }
             }
             __syncwarp();
@@ -349,11 +388,18 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             for (int p = tid; p < npairs; p += ntc) {
                 double d0 = 0.0, d1 = 0.0;
                 for (int k = 0; k < Sw; k++) { d0 += ysum[(size_t)(2 * p) * Sw + k]; d1 += ysum[(size_t)(2 * p + 1) * Sw + k]; }
-                epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt);
+                if (TP && a.epi == EPI_PARTIAL) {          // tensor-parallel K slice: unrounded, the exchange stage adds the shards
+                    a.y64[a.epi_row0 + r_begin + 2 * p] = d0;
+                    a.y64[a.epi_row0 + r_begin + 2 * p + 1] = d1;
+                } else {
+                    epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt);
+                }
             }
         }
-        if (tr) { tr[3] = global_ns(); tr[11] = (c_wait << 42) | ((c_dot & 0x1FFFFF) << 21) | (c_red & 0x1FFFFF); }     // warp 0: cycles waiting for tiles / in row dots / reducing
+        if (tr) tr[3] = global_ns();
     }
+    // every CTA read the exchange counter before its first grid barrier, CTA 0 is past the last one
+    if (TP && blockIdx.x == 0 && tid == 0) *reinterpret_cast<volatile unsigned*>(tp.epoch) = tp_epoch;
 }
 
 int g_mega_sms = 0;
@@ -361,20 +407,36 @@ int g_mega_sms = 0;
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------------------
-int mega_plan_stage(MegaStage& st, int ncw) {
+// Estimated consumer cost of a stage per row pair: (units per lane x 2 rows x ~27 instructions + the f64
+// butterfly, ~35) spread over the G row workers -- the model behind the choice of units per lane.
+static double plan_cost(int nunits, int nbe, int ncw, int* S_out, int* G_out) {
+    const int S = (nunits + 32 * nbe - 1) / (32 * nbe);
+    if (S > ncw) return 1e30;
+    const int G = ncw / S;
+    *S_out = S; *G_out = G;
+    return (54.0 * nbe + 35.0) / G;
+}
+double mega_plan_cost(const QMat& W, int nb_max) {
+    const bool kq = W.type == T_Q4_K || W.type == T_Q6_K;
+    const int nunits = (int)(kq ? W.k / 128 : W.k / 32);
+    double best = 1e30;
+    int S, G;
+    for (int nbe = kq ? 1 : nb_max; nbe >= 1; nbe--) best = std::min(best, plan_cost(nunits, nbe, MEGA_NCW, &S, &G));
+    return best * (double)(W.rows / 2);
+}
+int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
     const QMat& W = st.g.W;
     const bool kq = W.type == T_Q4_K || W.type == T_Q6_K;
-    const int nb_max = kq ? 1 : 4;
+    const int nb_max = kq ? 1 : nb_max_q;
     st.nunits = (int)(kq ? W.k / 128 : W.k / 32);
     // S warps cover a row (nbeff units per lane); G = ncw / S "row workers" take the rows of a tile
-    // round-robin.  Pick the units-per-lane that leaves the fewest warps, then lanes, idle.
+    // round-robin.  Pick the units-per-lane with the lowest estimated cost per row pair.
+    double best = 1e30;
     int best_idle = 1 << 30;
     for (int nbe = nb_max; nbe >= 1; nbe--) {
-        const int S = (st.nunits + 32 * nbe - 1) / (32 * nbe);
-        if (S > ncw) continue;
-        const int G = ncw / S;
-        const int idle = (ncw - G * S) * 1024 + (S * 32 * nbe - st.nunits);
-        if (idle < best_idle) { best_idle = idle; st.nbeff = nbe; st.S = S; st.G = G; }
+        int S = 0, G = 0;
+        const double c = plan_cost(st.nunits, nbe, ncw, &S, &G);
+        if (c < best) { best = c; best_idle = 0; st.nbeff = nbe; st.S = S; st.G = G; }
     }
     if (best_idle == (1 << 30)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: k=%lld does not map onto %d consumer warps", (long long)W.k, ncw);
     // tile = a whole number of worker rounds, close to 36 KB
@@ -387,9 +449,9 @@ int mega_plan_stage(MegaStage& st, int ncw) {
     return B2_OK;
 }
 
-template <int TYPE, int NB, int NCW, int GRP, int HD>
+template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
-    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD>;
+    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD, TP>;
     static PerDeviceSmem configured;
     if (configured.raise(L.smem_bytes)) {
         B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
@@ -410,13 +472,13 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     at[1].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp));
     return B2_OK;
 }
 
-template <int TYPE, int NB, int NCW, int GRP, int HD>
+template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
-    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD>;
+    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD, TP>;
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(L.cluster * 64);
@@ -431,11 +493,16 @@ static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
     return B2_OK;
 }
 
+#define B2_MEGA_CASE(FN, G, H, ...)                                                                        \
+    if (L.type == T_Q4_0 && L.grp == G && L.head_dim == H && L.nb == 4)                                    \
+        return L.tp.n > 1 ? FN<T_Q4_0, 4, MEGA_NCW, G, H, true>(__VA_ARGS__) : FN<T_Q4_0, 4, MEGA_NCW, G, H, false>(__VA_ARGS__); \
+    if (L.type == T_Q4_0 && L.grp == G && L.head_dim == H && L.nb == 5)                                    \
+        return L.tp.n > 1 ? FN<T_Q4_0, 5, MEGA_NCW, G, H, true>(__VA_ARGS__) : FN<T_Q4_0, 5, MEGA_NCW, G, H, false>(__VA_ARGS__)
 #define B2_MEGA_DISPATCH(FN, ...)                                                                          \
     do {                                                                                                   \
-        if (L.type == T_Q4_0 && L.grp == 1 && L.head_dim == 64) return FN<T_Q4_0, 4, MEGA_NCW, 1, 64>(__VA_ARGS__);   \
-        if (L.type == T_Q4_0 && L.grp == 1 && L.head_dim == 128) return FN<T_Q4_0, 4, MEGA_NCW, 1, 128>(__VA_ARGS__); \
-        if (L.type == T_Q4_0 && L.grp == 8 && L.head_dim == 128) return FN<T_Q4_0, 4, MEGA_NCW, 8, 128>(__VA_ARGS__); \
+        B2_MEGA_CASE(FN, 1, 64, __VA_ARGS__);                                                              \
+        B2_MEGA_CASE(FN, 1, 128, __VA_ARGS__);                                                             \
+        B2_MEGA_CASE(FN, 8, 128, __VA_ARGS__);                                                             \
     } while (0)
 
 bool mega_supported(int type, int grp, int head_dim) {

@@ -21,7 +21,7 @@ LOAD_NO_PDL, LOAD_NO_GRAPH, LOAD_NO_MEGA, LOAD_NO_BATCH = 1, 2, 4, 8
 # every symbol include/b2gguf.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
-    "b2_seq_new", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
+    "b2_seq_new", "b2_seq_assume", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
     "b2_get_stats", "b2_mega_trace", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemm", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
 ]
 
@@ -71,6 +71,7 @@ def lib() -> C.CDLL:
         L.b2_seq_free.argtypes = [vp, C.c_int]
         L.b2_seq_len.argtypes = [vp, C.c_int]
         L.b2_seq_truncate.argtypes = [vp, C.c_int, C.c_int]
+        L.b2_seq_assume.argtypes = [vp, C.c_int, C.c_int]
         L.b2_prefill.argtypes = [vp, C.c_int, vp, C.c_int, vp]
         L.b2_decode.argtypes = [vp, C.c_int, vp, vp, vp, vp]
         L.b2_decode_greedy.argtypes = [vp, C.c_int, C.c_int32, C.c_int, vp]
@@ -213,6 +214,9 @@ class Model:
             self.close()
         except Exception:
             pass
+
+    def seq_assume(self, seq: int, n_tokens: int) -> None:
+        _check(lib().b2_seq_assume(self._h, seq, n_tokens))
 
     def seq_new(self) -> int:
         s = C.c_int(-1)

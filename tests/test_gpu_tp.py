@@ -19,15 +19,17 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
-@pytest.mark.parametrize("preset,tp", [("tiny-llama", 2), ("tiny-gqa", 2), ("tiny-llama", 4)])
-def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp):
+@pytest.mark.parametrize("preset,tp,flags", [("tiny-llama", 2, 0), ("tiny-llama", 2, 4), ("tiny-gqa", 2, 0), ("tiny-llama", 4, 0), ("tiny-llama", 4, 6)])
+def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp, flags):
+    """flags 0: the persistent kernel with exchange stages (tiny-llama) or per-matrix kernels (tiny-gqa, mixed types);
+    4: per-matrix kernels + the all-reduce kernel; 6: the same without CUDA graphs."""
     if _n_gpus() < tp:
         pytest.skip(f"needs {tp} GPUs")
     E = pkg.engine
     path = pkg.synth.cached_model(preset, model_dir)
     e1, en = E.Engine(0), E.Engine(list(range(tp)))
     m1 = e1.load(path, max_batch=2, max_ctx=256)
-    mt = en.load(path, max_batch=2, max_ctx=256, tp_size=tp)
+    mt = en.load(path, max_batch=2, max_ctx=256, tp_size=tp, flags=flags)
     assert mt.info.n_head == m1.info.n_head and mt.info.step_weight_bytes >= m1.info.step_weight_bytes
     toks = pkg.synth.prompt_tokens(21, m1.info.n_vocab, seed=5)
     s1, st = m1.seq_new(), mt.seq_new()

@@ -37,7 +37,3 @@ for k, nm in ((0, "qkv"), (3, "up"), (4, "down")):
     pts = np.where(pts == 0, np.nan, pts)
     print(f"prologue {nm}: barrier->loads issued, ->x arrived+squares, ->stats, ->quantised, ->bar, ->xregs (us):", np.round(np.nanmean(np.diff(pts, axis=1), 0) / 1.9e3, 2), '(SM cycles / 1.9 GHz)')
 
-for k, nm in ((0, "qkv"), (2, "wo"), (3, "up"), (4, "down")):
-    v = tr[:, 15 * 5 + k, 11].astype(np.uint64)
-    wait, dot, red = (v >> np.uint64(42)).astype(np.float64), ((v >> np.uint64(21)) & np.uint64(0x1FFFFF)).astype(np.float64), (v & np.uint64(0x1FFFFF)).astype(np.float64)
-    print(f"body {nm}: warp 0 cycles per stage (mean over CTAs, us at 1.9 GHz): waiting for tiles {wait.mean()/1.9e3:.2f}, row dots {dot.mean()/1.9e3:.2f}, reduction+store {red.mean()/1.9e3:.2f}")

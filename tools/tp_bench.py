@@ -28,7 +28,11 @@ for tp in tps:
     info = m.info
     s = m.seq_new()
     t0 = time.time()
-    m.prefill(s, p.synth.prompt_tokens(ctx, info.n_vocab))
+    if os.environ.get("TP_BENCH_ASSUME"):       # synthetic context: the (zeroed) cache rows are declared valid, only a short prompt is evaluated
+        m.seq_assume(s, ctx - 16)
+        m.prefill(s, p.synth.prompt_tokens(16, info.n_vocab))
+    else:
+        m.prefill(s, p.synth.prompt_tokens(ctx, info.n_vocab))
     pre_s = time.time() - t0
     m.decode_greedy(s, 8)
     toks = m.decode_greedy(s, steps)
