@@ -119,7 +119,10 @@ __device__ __forceinline__ int reduce8_index(int lane) { return ((lane >> 4) & 1
 template <int GRP, int HD, int NT>
 static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCfg& c, int kvh, uint8_t* smem_raw, int tid, uint64_t* xb, uint32_t& xphase,
                                                  int barid, int pos_value = -1, const int* page_table_override = nullptr,
-                                                 unsigned long long* tr = nullptr) {
+                                                 unsigned long long* tr = nullptr, int kv_index = -1) {
+    // kvh indexes the query-head group (q and out); kv_index, when given, the KV head whose cache rows are read:
+    // a GQA group can be processed one query head at a time (GRP = 1, kvh = query head, kv_index = its KV head)
+    // by different clusters -- every (head, position) product is computed the same way, so the bits do not change.
     auto stamp = [&](int k) { if (tr) tr[k] = (unsigned long long)clock64(); };
     stamp(0);
     constexpr int NWARP = NT / 32;
@@ -133,8 +136,8 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     const int* page_table = page_table_override ? page_table_override : a.page_table;
     const int n = (pos_value >= 0 ? pos_value : *a.pos) + 1;
     // operands into registers once (the descriptor lives in global memory)
-    const __half* const k_base = a.k_base + (size_t)kvh * HD;
-    const __half* const v_base = a.v_base + (size_t)kvh * HD;
+    const __half* const k_base = a.k_base + (size_t)(kv_index >= 0 ? kv_index : kvh) * HD;
+    const __half* const v_base = a.v_base + (size_t)(kv_index >= 0 ? kv_index : kvh) * HD;
     const float scale = a.scale;
     const int kv_dim = a.kv_dim, pshift = __ffs(a.page_tokens) - 1, pmask = a.page_tokens - 1;      // pages are a power of two
 

@@ -226,8 +226,14 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             ac.cluster = cluster_size;
             ac.max_local = S.att_max_local;
             const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
-            for (int kvh = my_cluster; kvh < a.n_head_kv; kvh += n_clusters)
-                attn_kv_head<GRP, HD, ntc>(a, ac, kvh, att_smem, tid, xbar, xphase, 1, pos_now, s_pt, tr ? tr + 4 : nullptr);
+            if (GRP > 1 && 2 * a.n_head_kv <= n_clusters) {
+                // few KV heads (GQA under tensor parallelism): one query head per cluster instead of one group
+                for (int h = my_cluster; h < a.n_head; h += n_clusters)
+                    attn_kv_head<1, HD, ntc>(a, ac, h, att_smem, tid, xbar, xphase, 1, pos_now, s_pt, tr ? tr + 4 : nullptr, h / GRP);
+            } else {
+                for (int kvh = my_cluster; kvh < a.n_head_kv; kvh += n_clusters)
+                    attn_kv_head<GRP, HD, ntc>(a, ac, kvh, att_smem, tid, xbar, xphase, 1, pos_now, s_pt, tr ? tr + 4 : nullptr);
+            }
             if (tr) tr[2] = tr[3] = global_ns();
             continue;
         }

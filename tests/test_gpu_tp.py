@@ -19,7 +19,7 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
-@pytest.mark.parametrize("preset,tp,flags", [("tiny-llama", 2, 0), ("tiny-llama", 2, 4), ("tiny-gqa", 2, 0), ("tiny-llama", 4, 0), ("tiny-llama", 4, 6)])
+@pytest.mark.parametrize("preset,tp,flags", [("tiny-llama", 2, 0), ("tiny-llama", 2, 4), ("tiny-gqa", 2, 0), ("tiny-gqa8", 2, 0), ("tiny-llama", 4, 0), ("tiny-llama", 4, 6)])
 def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp, flags):
     """flags 0: the persistent kernel with exchange stages (tiny-llama) or per-matrix kernels (tiny-gqa, mixed types);
     4: per-matrix kernels + the all-reduce kernel; 6: the same without CUDA graphs."""
