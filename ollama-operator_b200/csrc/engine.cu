@@ -550,14 +550,15 @@ int Model::setup_mega(Slot& s) {
             if (op.g.W.type != type) return B2_OK;          // mixed tensor types: per-matrix kernels
         }
     const int grp = hp.n_head / hp.n_head_kv;
-    if (!mega_supported(type, grp, hp.head_dim)) return B2_OK;
+    if (!mega_supported(type, grp, hp.head_dim) || (tp_size > 1 && hp.head_dim == 80)) return B2_OK;
     std::vector<MegaStage> st;
     int64_t k_max = 0;
     size_t tile_max = 0;
     int rt_s_max = 0;
     MegaLaunch& L = s.mega;
     L = MegaLaunch();
-    L.type = type; L.grp = grp; L.head_dim = hp.head_dim; L.cluster = 4;
+    L.type = type; L.grp = grp; L.head_dim = hp.head_dim;
+    L.cluster = hp.head_dim % 32 == 0 ? 4 : 2;      // the output dims of a head are split eight per warp over the cluster's CTAs (phi-2: 80 = 2 x 40)
     L.tp = tp;
     if (const char* v = getenv("B2_MEGA_CLUSTER")) L.cluster = atoi(v);
     {   // kernel variant: 4 or 5 activation units per lane (K = 5120 needs 5 to keep one warp per row)

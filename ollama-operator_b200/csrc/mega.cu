@@ -504,15 +504,21 @@ static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
         return L.tp.n > 1 ? FN<T_Q4_0, 4, MEGA_NCW, G, H, true>(__VA_ARGS__) : FN<T_Q4_0, 4, MEGA_NCW, G, H, false>(__VA_ARGS__); \
     if (L.type == T_Q4_0 && L.grp == G && L.head_dim == H && L.nb == 5)                                    \
         return L.tp.n > 1 ? FN<T_Q4_0, 5, MEGA_NCW, G, H, true>(__VA_ARGS__) : FN<T_Q4_0, 5, MEGA_NCW, G, H, false>(__VA_ARGS__)
+#define B2_MEGA_CASE_1GPU(FN, G, H, ...)                                                                   \
+    if (L.type == T_Q4_0 && L.grp == G && L.head_dim == H && L.tp.n <= 1) {                                \
+        if (L.nb == 4) return FN<T_Q4_0, 4, MEGA_NCW, G, H, false>(__VA_ARGS__);                           \
+        if (L.nb == 5) return FN<T_Q4_0, 5, MEGA_NCW, G, H, false>(__VA_ARGS__);                           \
+    }
 #define B2_MEGA_DISPATCH(FN, ...)                                                                          \
     do {                                                                                                   \
+        B2_MEGA_CASE_1GPU(FN, 1, 80, __VA_ARGS__);                                                         \
         B2_MEGA_CASE(FN, 1, 64, __VA_ARGS__);                                                              \
         B2_MEGA_CASE(FN, 1, 128, __VA_ARGS__);                                                             \
         B2_MEGA_CASE(FN, 8, 128, __VA_ARGS__);                                                             \
     } while (0)
 
 bool mega_supported(int type, int grp, int head_dim) {
-    return type == T_Q4_0 && ((grp == 1 && (head_dim == 64 || head_dim == 128)) || (grp == 8 && head_dim == 128));
+    return type == T_Q4_0 && ((grp == 1 && (head_dim == 64 || head_dim == 80 || head_dim == 128)) || (grp == 8 && head_dim == 128));
 }
 
 // Fill in the shared-memory layout and the grid for a model: k_max = longest activation vector,
