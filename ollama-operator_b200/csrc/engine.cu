@@ -546,11 +546,18 @@ int Model::setup_mega(Slot& s) {
     int type = -1;
     for (const StepOp& op : s.ops)
         if (op.kind == 0) {
-            if (type < 0) type = op.g.W.type;
-            if (op.g.W.type != type) return B2_OK;          // mixed tensor types: per-matrix kernels
+            const int t = op.g.W.type == T_Q4_K || op.g.W.type == T_Q6_K ? T_KQ : op.g.W.type;      // Q4_K_M mixes the two K-quants
+            if (type < 0) type = t;
+            if (t != type) {          // other mixtures: per-matrix kernels
+                if (getenv("B2_MEGA_VERBOSE")) fprintf(stderr, "b2: persistent kernel not used: tensor types %d and %d in one model\n", type, t);
+                return B2_OK;
+            }
         }
     const int grp = hp.n_head / hp.n_head_kv;
-    if (!mega_supported(type, grp, hp.head_dim) || (tp_size > 1 && hp.head_dim == 80)) return B2_OK;
+    if (!mega_supported(type, grp, hp.head_dim) || (tp_size > 1 && hp.head_dim == 80)) {
+        if (getenv("B2_MEGA_VERBOSE")) fprintf(stderr, "b2: persistent kernel not used: no variant for type %d, %d query heads per KV head, head_dim %d\n", type, grp, hp.head_dim);
+        return B2_OK;
+    }
     std::vector<MegaStage> st;
     int64_t k_max = 0;
     size_t tile_max = 0;
@@ -592,6 +599,7 @@ int Model::setup_mega(Slot& s) {
         }
     }
     if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) {
+        if (getenv("B2_MEGA_VERBOSE")) fprintf(stderr, "b2: persistent kernel not used: %s\n", last_error());
         cudaGetLastError();          // does not fit: keep the per-matrix path, and leave no stale CUDA error behind
         return B2_OK;
     }

@@ -25,6 +25,7 @@
 namespace b2 {
 
 enum GgmlType : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q6_K = 14 };
+constexpr int T_KQ = 100;      // persistent-kernel variant for K-quant models: every matrix is Q4_K or Q6_K (Q4_K_M mixes them)
 
 #pragma pack(push, 1)
 struct BlockQ4_0 { uint16_t d; uint8_t qs[16]; };

@@ -190,7 +190,7 @@ template <int TYPE> struct XRegs;
 
 template <> struct XRegs<T_Q4_0> {
     uint4 a, b; float d; int s8;
-    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int nunits, bool valid) {
+    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int nunits, bool valid, int = 0) {
         if (valid) {
             a = *reinterpret_cast<const uint4*>(xq + u * 16);
             b = *reinterpret_cast<const uint4*>(xq + nunits * 16 + u * 16);
@@ -200,7 +200,7 @@ template <> struct XRegs<T_Q4_0> {
 };
 template <> struct XRegs<T_Q8_0> {
     uint4 a, b; float d;
-    __device__ void load(const uint8_t* xq, const float* xd, const int*, int u, int nunits, bool valid) {
+    __device__ void load(const uint8_t* xq, const float* xd, const int*, int u, int nunits, bool valid, int = 0) {
         if (valid) {
             a = *reinterpret_cast<const uint4*>(xq + u * 16);
             b = *reinterpret_cast<const uint4*>(xq + nunits * 16 + u * 16);
@@ -210,7 +210,7 @@ template <> struct XRegs<T_Q8_0> {
 };
 template <> struct XRegs<T_Q6_K> {
     uint32_t w[32]; int bs32[8]; float d;
-    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int, bool valid) {
+    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int, bool valid, int = 0) {
         if (valid) {
 #pragma unroll
             for (int i = 0; i < 8; i++) {
@@ -231,7 +231,7 @@ template <> struct XRegs<T_Q6_K> {
 };
 template <> struct XRegs<T_Q4_K> {
     uint32_t w[32]; int bs[4]; float d;
-    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int, bool valid) {
+    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int, bool valid, int = 0) {
         if (valid) {
 #pragma unroll
             for (int i = 0; i < 8; i++) {
@@ -246,6 +246,35 @@ template <> struct XRegs<T_Q4_K> {
             for (int i = 0; i < 32; i++) w[i] = 0;
 #pragma unroll
             for (int j = 0; j < 4; j++) bs[j] = 0;
+            d = 0.f;
+        }
+    }
+};
+
+// Either K-quant, chosen per matrix at run time (warp-uniform): the same registers serve both layouts.
+template <> struct XRegs<T_KQ> {
+    uint32_t w[32]; int bs[8]; float d; int type;
+    __device__ void load(const uint8_t* xq, const float* xd, const int* xs, int u, int, bool valid, int t) {
+        type = t;
+        if (valid) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint4 q = *reinterpret_cast<const uint4*>(xq + u * 128 + i * 16);
+                w[4 * i] = q.x; w[4 * i + 1] = q.y; w[4 * i + 2] = q.z; w[4 * i + 3] = q.w;
+            }
+            if (t == T_Q6_K) {
+#pragma unroll
+                for (int g = 0; g < 8; g++) bs[g] = 32 * xs[u * 8 + g];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) { bs[j] = xs[u * 8 + 2 * j] + xs[u * 8 + 2 * j + 1]; bs[4 + j] = 0; }
+            }
+            d = xd[u >> 1];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) w[i] = 0;
+#pragma unroll
+            for (int g = 0; g < 8; g++) bs[g] = 0;
             d = 0.f;
         }
     }
@@ -358,6 +387,25 @@ __device__ __forceinline__ float unit_dot(const XRegs<T_Q4_K>& x, const RowPtrs&
     }
     const float d = __fmul_rn(__low2float(dm), x.d), dmin = __fmul_rn(__high2float(dm), x.d);
     return __fsub_rn(__fmul_rn(d, (float)accs), __fmul_rn(dmin, (float)accm));
+}
+
+__device__ __forceinline__ float unit_dot(const XRegs<T_KQ>& x, const RowPtrs& r, int u, int nunits) {
+    if (x.type == T_Q6_K) {
+        XRegs<T_Q6_K> t;
+#pragma unroll
+        for (int i = 0; i < 32; i++) t.w[i] = x.w[i];
+#pragma unroll
+        for (int g = 0; g < 8; g++) t.bs32[g] = x.bs[g];
+        t.d = x.d;
+        return unit_dot(t, r, u, nunits);
+    }
+    XRegs<T_Q4_K> t;
+#pragma unroll
+    for (int i = 0; i < 32; i++) t.w[i] = x.w[i];
+#pragma unroll
+    for (int j = 0; j < 4; j++) t.bs[j] = x.bs[j];
+    t.d = x.d;
+    return unit_dot(t, r, u, nunits);
 }
 
 // ---------------------------------------------------------------------------------------------

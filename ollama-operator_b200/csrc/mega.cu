@@ -115,7 +115,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int ntc = NCW * 32;
-    constexpr int NP = TYPE == T_Q4_0 || TYPE == T_Q8_0 ? 2 : TYPE == T_Q4_K ? 3 : 4;
+    constexpr int NP = TYPE == T_Q4_0 || TYPE == T_Q8_0 ? 2 : TYPE == T_Q4_K ? 3 : 4;      // T_KQ: up to 4, the matrix says how many
     const int cluster_size = (int)cluster_nctarank();
     // position and page table of this step: fetched once, used by every layer's KV append and attention
     __shared__ int s_pos;
@@ -167,6 +167,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     const int rows_here = (int)min((int64_t)p.RT, p.r_end - p.row0);
 #pragma unroll
                     for (int pl = 0; pl < NP; pl++) {
+                        if (TYPE == T_KQ && pl >= W.n_planes) break;
                         prefetch_l2(W.plane[pl] + (size_t)p.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl]);
                         ahead += (long long)rows_here * W.stride[pl];
                     }
@@ -178,11 +179,13 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 const int rows_here = (int)min((int64_t)f.RT, f.r_end - f.row0);
                 uint32_t total = 0;
 #pragma unroll
-                for (int pl = 0; pl < NP; pl++) total += (uint32_t)rows_here * W.stride[pl];
+                for (int pl = 0; pl < NP; pl++)
+                    if (TYPE != T_KQ || pl < W.n_planes) total += (uint32_t)rows_here * W.stride[pl];
                 mbar_expect_tx(&full[s], total);
                 uint8_t* dst = ring + (size_t)s * sm.stage_bytes;
 #pragma unroll
                 for (int pl = 0; pl < NP; pl++) {
+                    if (TYPE == T_KQ && pl >= W.n_planes) break;
                     bulk_g2s(dst, W.plane[pl] + (size_t)f.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl], &full[s], pol);
                     dst += (size_t)f.RT * W.stride[pl];
                 }
@@ -331,7 +334,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             const int u = (ch * nbeff + j) * 32 + lane;
             const bool valid = working && j < nbeff && u < nunits;
             unit[j] = u < nunits ? u : nunits - 1;
-            xr[j].load(xq, xd, xs, unit[j], nunits, valid);
+            xr[j].load(xq, xd, xs, unit[j], nunits, valid, a.W.type);
         }
         if (tr) { tr[2] = global_ns(); tr[9] = (unsigned long long)clock64(); }
         // the attention stage that follows will read K/V rows that already exist: pull them into L2
@@ -348,7 +351,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         // the row loop needs in registers
         uint32_t wstride[NP];
 #pragma unroll
-        for (int p = 0; p < NP; p++) wstride[p] = (uint32_t)a.W.stride[p];
+        for (int p = 0; p < NP; p++) wstride[p] = TYPE != T_KQ || p < a.W.n_planes ? (uint32_t)a.W.stride[p] : 0u;
         for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
             const uint32_t s = it % sm.ns;
             if (!(sm.debug & 2)) mbar_wait(&full[s], (it / sm.ns) & 1);
@@ -451,6 +454,7 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
     int rounds = (int)((40 * 1024) / (rb * st.G * 2));
     if (rounds < 1) rounds = 1;
     st.RT = rounds * st.G * 2;           // every worker takes two rows per round
+    while ((size_t)st.RT * rb > 72 * 1024 && st.RT > 2) st.RT -= 2;      // heavy rows (Q6_K): two stages must still fit the ring; some workers idle
     st.P = 1; st.RPG = 0;
     return B2_OK;
 }
@@ -509,8 +513,12 @@ static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
         if (L.nb == 4) return FN<T_Q4_0, 4, MEGA_NCW, G, H, false>(__VA_ARGS__);                           \
         if (L.nb == 5) return FN<T_Q4_0, 5, MEGA_NCW, G, H, false>(__VA_ARGS__);                           \
     }
+#define B2_MEGA_CASE_KQ(FN, G, H, ...)                                                                     \
+    if (L.type == T_KQ && L.grp == G && L.head_dim == H && L.tp.n <= 1) return FN<T_KQ, 1, MEGA_NCW, G, H, false>(__VA_ARGS__)
 #define B2_MEGA_DISPATCH(FN, ...)                                                                          \
     do {                                                                                                   \
+        B2_MEGA_CASE_KQ(FN, 4, 64, __VA_ARGS__);                                                           \
+        B2_MEGA_CASE_KQ(FN, 4, 128, __VA_ARGS__);                                                          \
         B2_MEGA_CASE_1GPU(FN, 1, 80, __VA_ARGS__);                                                         \
         B2_MEGA_CASE(FN, 1, 64, __VA_ARGS__);                                                              \
         B2_MEGA_CASE(FN, 1, 128, __VA_ARGS__);                                                             \
@@ -518,6 +526,7 @@ static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
     } while (0)
 
 bool mega_supported(int type, int grp, int head_dim) {
+    if (type == T_KQ) return grp == 4 && (head_dim == 64 || head_dim == 128);
     return type == T_Q4_0 && ((grp == 1 && (head_dim == 64 || head_dim == 80 || head_dim == 128)) || (grp == 8 && head_dim == 128));
 }
 
@@ -525,7 +534,7 @@ bool mega_supported(int type, int grp, int head_dim) {
 // row_bytes_max = bytes of the largest stage tile row set (RT rows).
 int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx) {
     if (!mega_supported(L.type, L.grp, L.head_dim)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: no kernel for type %d, %d query heads per KV head, head_dim %d", L.type, L.grp, L.head_dim);
-    const bool kq = L.type == T_Q4_K || L.type == T_Q6_K;
+    const bool kq = L.type == T_Q4_K || L.type == T_Q6_K || L.type == T_KQ;
     size_t off = (2 * MEGA_NS_MAX + 2) * 8 + 32 * 8;
     L.off_red = (uint32_t)off; off += (size_t)2 * rt_s_max * 8; off = (off + 15) / 16 * 16;
     L.off_xq = (uint32_t)off; off += (size_t)k_max; off = (off + 15) / 16 * 16;
