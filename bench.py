@@ -12,10 +12,12 @@ scaling, no data-path collective; `value` is the sum over replicas.
 
   value   device-resident greedy loop (b2_decode_greedy): tokens, positions and KV stay in HBM
   e2e     the same steps through b2_decode with HOST token buffers (H2D + D2H every step)
-  roofline dominant kernel = the fused W4A8 GEMV; achieved = weight bytes of the largest
-          per-layer matrix (gate|up, 22016x4096 Q4_0) / its mean launch time, timed alone
-          with CUDA events on its stream, against the measured burst HBM peak; `step` adds
-          the whole-step figure against the same peak
+  roofline dominant kernel = the persistent all-layers kernel (one launch per step); achieved =
+          its algorithmic bytes (layer weights + the KV rows attention reads) / its launch
+          duration, measured live with CUDA events on the engine's stream (b2_profile_step),
+          against the measured burst HBM peak; `step` adds the whole-step figure
+  prefill, batch32  the other half of configs[1]: the 512-token prompt through the batched
+          kernels, and 32 sequences decoded together through b2_decode
   cpu_baseline  the CPU oracle (oracle/ggml_ref.c, a port of the llama.cpp CPU path) timed on
           the host cores for a bounded sample of the same workload; also used to check the
           GPU logits/tokens at full model size
@@ -43,6 +45,21 @@ UNIT = "tok/s"
 
 def pkg():
     return importlib.import_module("ollama-operator_b200")
+
+
+def job_times(local_ms, dist=None, device="cpu"):
+    """Whole-job duration of every timed region: the MAX over ranks (the replicas run side by side,
+    the job is done when the slowest is).  local_ms: this rank's milliseconds per region."""
+    import torch
+    t = torch.tensor(list(local_ms), dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t]
+
+
+def whole_job_rate(world, steps_per_rank, ms):
+    """Units all ranks processed divided by the job's duration (weak scaling: every rank does steps_per_rank)."""
+    return world * steps_per_rank / (ms / 1e3)
 
 
 def oracle_mod():
@@ -215,18 +232,15 @@ def run_gpu(args):
     sampler.window_end()
     clocks = sampler.stop()       # samples span both timed regions (device-resident loop and end-to-end loop)
 
-    tmax = torch.tensor([gpu_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
-    if dist:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    gpu_ms_max, e2e_ms_max = float(tmax[0]), float(tmax[1])
+    gpu_ms_max, e2e_ms_max = job_times([gpu_ms, e2e_s * 1e3], dist, f"cuda:{local}")
     if rank != 0:
         m.close(); eng.close()
         if dist:
             dist.destroy_process_group()
         return
 
-    value = world * args.steps / (gpu_ms_max / 1e3)
-    e2e = world * args.steps / (e2e_ms_max / 1e3)
+    value = whole_job_rate(world, args.steps, gpu_ms_max)
+    e2e = whole_job_rate(world, args.steps, e2e_ms_max)
     peak, peak_src = peaks()
     # ---- dominant kernel ----------------------------------------------------------------------------------
     # With the persistent kernel one launch per step does all layers: its duration is measured live with
