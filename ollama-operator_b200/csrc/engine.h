@@ -102,7 +102,7 @@ struct Model {
     void* slot_mem = nullptr;
     std::vector<Slot> slots;
     BatchCtx bt;
-    int batch_min_seqs = 5;           // b2_decode switches to the batched kernels from this many sequences
+    int batch_min_seqs = 3;           // b2_decode switches to the batched kernels from this many sequences
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     size_t weight_bytes = 0, step_weight_bytes = 0;

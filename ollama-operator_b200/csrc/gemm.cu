@@ -152,12 +152,15 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
     }
 
     // ===== consumers =====
-    // Work units are (row tile, 8-column tile) pairs; warp w owns units w, w+8, ... (warps w and w+4 share an
-    // SM sub-partition, so the four schedulers carry the same load for the usual 20 or 24 units).
+    // Work units are (row tile, 8-column tile) pairs; warp w owns units w, w+16, ... (warps w and w+4 share an
+    // SM sub-partition, so the four schedulers carry the same load for the usual 20 or 24 units).  With few
+    // units (small batches, narrow matrices) two warps share a unit, each taking one half of every K chunk;
+    // their f64 partial sums meet in shared memory, in a fixed order.
     const int g = lane >> 2, t = lane & 3;
     uint32_t it = 0;
     for (int grp = 0; grp < n_grp; grp++) {
         const int gt0 = t0 + grp * per, n_rt = min(per, t1 - gt0), tot = n_rt * NT;
+        const int KS = NT <= 2 && 2 * tot <= GB_WARPS ? 2 : 1;      // (compiled out for wide batches: their units keep every warp busy)
         double acc[GB_MAXI][4];
 #pragma unroll
         for (int m = 0; m < GB_MAXI; m++)
@@ -170,15 +173,17 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
             const int nsub = min(2, (nbk - kc * GEMM_KC) >> 3);
 #pragma unroll
             for (int m = 0; m < GB_MAXI; m++) {
-                const int unit = warp + GB_WARPS * m;
-                if (unit < tot) {
+                const int u = warp + GB_WARPS * m;
+                if (u < tot * KS) {
+                    const int unit = u % tot, ks = u / tot;
                     const int rt = unit / NT, j = unit - rt * NT;
                     const uint8_t* qb = sb + rt * 2 * GB_QBOX + g * 128 + 4 * t;
                     const uint8_t* db = sb + GB_OFF_D + rt * GB_DBOX + g * (GEMM_KC * 2);
                     const uint8_t* xc = sb + GB_OFF_XQ + (8 * j + g) * GEMM_XCOL + 4 * t;
                     const float2* xdp = reinterpret_cast<const float2*>(sb + GB_OFF_XD) + 4 * j + t;     // [b][32] floats: pair (c0, c0+1), c0 = 8j + 2t
                     const int2* xsp = reinterpret_cast<const int2*>(sb + GB_OFF_XS) + 4 * j + t;
-                    for (int sub = 0; sub < nsub; sub++) {
+                    const int sub_begin = KS == 2 ? ks : 0, sub_end = KS == 2 ? min(nsub, ks + 1) : nsub;
+                    for (int sub = sub_begin; sub < sub_end; sub++) {
                         const uint4 dv0 = *reinterpret_cast<const uint4*>(db + sub * 16);
                         const uint4 dv1 = *reinterpret_cast<const uint4*>(db + 8 * (GEMM_KC * 2) + sub * 16);
                         const uint32_t dw0p[4] = {dv0.x, dv0.y, dv0.z, dv0.w}, dw1p[4] = {dv1.x, dv1.y, dv1.z, dv1.w};
@@ -206,14 +211,22 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
             if (lane == 0) mbar_arrive(&empty[s]);
         }
         // results of the row group -> shared memory -> the GEMV's epilogues with each column's operands
+        double* outd = reinterpret_cast<double*>(outb);        // KS == 2: [ks][unit][4][32] partial sums
+        if (KS == 2) {
+            if (warp < tot * 2) {
 #pragma unroll
-        for (int m = 0; m < GB_MAXI; m++) {
-            const int unit = warp + GB_WARPS * m;
-            if (unit < tot) {
-                const int rt = unit / NT, j = unit - rt * NT;
-                float* o = outb + (rt * 16 + g) * GB_OUT_STRIDE + 8 * j + 2 * t;
-                o[0] = (float)acc[m][0]; o[1] = (float)acc[m][1];
-                o[8 * GB_OUT_STRIDE] = (float)acc[m][2]; o[8 * GB_OUT_STRIDE + 1] = (float)acc[m][3];
+                for (int q = 0; q < 4; q++) outd[(warp * 4 + q) * 32 + lane] = acc[0][q];      // u = warp: ks = warp / tot, unit = warp % tot
+            }
+        } else {
+#pragma unroll
+            for (int m = 0; m < GB_MAXI; m++) {
+                const int unit = warp + GB_WARPS * m;
+                if (unit < tot) {
+                    const int rt = unit / NT, j = unit - rt * NT;
+                    float* o = outb + (rt * 16 + g) * GB_OUT_STRIDE + 8 * j + 2 * t;
+                    o[0] = (float)acc[m][0]; o[1] = (float)acc[m][1];
+                    o[8 * GB_OUT_STRIDE] = (float)acc[m][2]; o[8 * GB_OUT_STRIDE + 1] = (float)acc[m][3];
+                }
             }
         }
         named_bar_sync(1, GB_NTC);
@@ -222,10 +235,21 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
             const int p = i / B, c = i - p * B;
             const int64_t r0 = (int64_t)gt0 * 16 + 2 * p;
             if (r0 < rows) {
+                float v0, v1;
+                if (KS == 2) {
+                    // rows 2p, 2p+1 of the group, column c: unit, lane and register of the MMA accumulator layout
+                    const int rl = 2 * p, unit = (rl >> 4) * NT + (c >> 3), ln = (rl & 7) * 4 + ((c & 7) >> 1), q = ((rl & 8) ? 2 : 0) + (c & 1);
+                    const double* p0 = outd + (unit * 4 + q) * 32 + ln;
+                    const double* p1 = outd + ((tot + unit) * 4 + q) * 32 + ln;
+                    v0 = (float)(p0[0] + p1[0]);
+                    v1 = (float)(p0[4] + p1[4]);            // row + 1: the next lane group (g + 1), same column
+                } else {
+                    v0 = outb[(2 * p) * GB_OUT_STRIDE + c];
+                    v1 = outb[(2 * p + 1) * GB_OUT_STRIDE + c];
+                }
                 unsigned long long best = 0ull;
                 const GemvArgs& a = colargs[c];
-                epilogue_pair(a, a.epi_row0 + r0, outb[(2 * p) * GB_OUT_STRIDE + c], outb[(2 * p + 1) * GB_OUT_STRIDE + c], best, col_pos[c],
-                              col_pt + (size_t)c * pt_stride);
+                epilogue_pair(a, a.epi_row0 + r0, v0, v1, best, col_pos[c], col_pt + (size_t)c * pt_stride);
                 if (a.epi == EPI_LOGITS && best != 0ull) atomicMax(a.argmax_key, best);
             }
         }

@@ -18,7 +18,7 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
-@pytest.mark.parametrize("preset,n_prompt", [("tiny-llama", 5), ("tiny-llama", 32), ("tiny-llama", 33), ("tiny-llama", 101), ("tiny-phi2", 70)])
+@pytest.mark.parametrize("preset,n_prompt", [("tiny-llama", 3), ("tiny-llama", 32), ("tiny-llama", 33), ("tiny-llama", 101), ("tiny-phi2", 70)])
 def test_chunked_prefill_equals_token_by_token(pkg, eng, model_dir, preset, n_prompt):
     E = pkg.engine
     path = pkg.synth.cached_model(preset, model_dir)
@@ -27,7 +27,7 @@ def test_chunked_prefill_equals_token_by_token(pkg, eng, model_dir, preset, n_pr
     toks = pkg.synth.prompt_tokens(n_prompt, ma.info.n_vocab, seed=n_prompt)
     sa, sb = ma.seq_new(), mb.seq_new()
     la, lb = ma.prefill(sa, toks), mb.prefill(sb, toks)
-    assert ma.stats().last_steps < n_prompt or n_prompt < 5        # the chunked path really ran
+    assert ma.stats().last_steps < n_prompt or n_prompt < 3        # the chunked path really ran
     assert mb.stats().last_steps == n_prompt
     assert np.array_equal(_bits(la), _bits(lb)), np.abs(la - lb).max()
     for layer in range(ma.info.n_layer):
@@ -41,7 +41,7 @@ def test_chunked_prefill_equals_token_by_token(pkg, eng, model_dir, preset, n_pr
     ma.close(); mb.close()
 
 
-@pytest.mark.parametrize("preset,n_seq", [("tiny-llama", 5), ("tiny-llama", 8), ("tiny-llama", 32), ("tiny-llama", 37), ("tiny-phi2", 5)])
+@pytest.mark.parametrize("preset,n_seq", [("tiny-llama", 3), ("tiny-llama", 8), ("tiny-llama", 32), ("tiny-llama", 37), ("tiny-phi2", 5)])
 def test_batched_decode_equals_sequential(pkg, eng, model_dir, preset, n_seq):
     E = pkg.engine
     path = pkg.synth.cached_model(preset, model_dir)
