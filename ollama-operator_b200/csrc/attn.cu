@@ -16,6 +16,7 @@
 // through DSMEM (one exchange).  Output: head dimension split over the CTAs, no merge.  No global
 // scratch, no second kernel.  HBM traffic is K and V once: (pos+1) * kv_dim * 2 * 2 bytes.
 #include <math.h>
+#include <stdlib.h>
 
 #include "attn_dev.cuh"
 #include "common.cuh"
@@ -83,6 +84,179 @@ int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg
     return B2_OK;
 }
 
+// ---- batched steps with many (column, head) pairs: one CTA per pair, K and V staged through shared memory -----
+// The cluster kernel above is organised around one sequence's latency; a batched step is bandwidth work (every
+// column brings its own KV rows: 268 MB per 7B layer at 32 x 512 tokens).  Here the rows of a 64-position chunk
+// are copied with cp.async (no registers held while in flight, the next chunk streams while this one is used),
+// and the arithmetic is attn_kv_head's, primitive for primitive and in the same order: q.K in the 32-lane SIMD
+// order through reduce8_lanes32 (tail dims in f64), one max, exp from f64, f64 sum, f16 probabilities, P.V as one
+// f32 FMA chain per (position mod 32, dim) in position order.  Same bits.
+constexpr int ABT = 64;                       // positions per chunk
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int HD>
+__global__ void __launch_bounds__(256) attn_batch_staged_kernel(const AttnArgs* __restrict__ args, const int maxc) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    constexpr int NT = 256, NWARP = 8, HD32 = HD & ~31, NI = HD32 / 32;
+    constexpr int ROWB = HD * 2 + 16;          // padded row: 16-byte reads of 32 different rows spread over the banks
+    constexpr int PIECES = HD * 2 / 16;        // 16-byte pieces per row
+    pdl_trigger();
+    pdl_wait();                                // q and this step's K/V rows come from the preceding kernel
+    const AttnArgs a = args[blockIdx.y];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = *a.pos + 1, h = blockIdx.x, kvh = h / (a.n_head / a.n_head_kv);
+    int* rowoff = reinterpret_cast<int*>(smem_raw);                      // [maxc]
+    float* sc = reinterpret_cast<float*>(smem_raw) + maxc;               // [maxc]
+    float* qs = sc + maxc;                                               // [HD]
+    float* red = qs + HD;                                                // [NWARP] floats, then [NWARP] doubles (16-byte aligned below)
+    double* redd = reinterpret_cast<double*>(red + NWARP);
+    uint8_t* tile = reinterpret_cast<uint8_t*>(redd + NWARP);            // [2][ABT][ROWB]
+    const int pshift = __ffs(a.page_tokens) - 1, pmask = a.page_tokens - 1;
+    for (int t = tid; t < n; t += NT) rowoff[t] = ((a.page_table[t >> pshift] << pshift) + (t & pmask)) * a.kv_dim;
+    for (int i = tid; i < HD; i += NT) qs[i] = __half2float(__float2half_rn(__ldcg(a.q + (size_t)h * HD + i)));
+    __syncthreads();
+    const int n_chunks = (n + ABT - 1) / ABT;
+    auto stage = [&](const __half* base, int c) {          // rows [c*ABT, c*ABT + ABT) of this head -> tile[c & 1]
+        uint8_t* dst = tile + (size_t)(c & 1) * ABT * ROWB;
+        for (int i = tid; i < ABT * PIECES; i += NT) {
+            const int r = i / PIECES, pc = i - r * PIECES, t = min(c * ABT + r, n - 1);
+            cp_async16(dst + r * ROWB + pc * 16, base + rowoff[t] + pc * 8);
+        }
+        cp_async_commit();
+    };
+
+    // ---- 1. scores ----
+    {
+        const __half* const k_base = a.k_base + (size_t)kvh * HD;
+        float qreg[NI];
+#pragma unroll
+        for (int i = 0; i < NI; i++) qreg[i] = qs[i * 32 + lane];
+        stage(k_base, 0);
+        for (int c = 0; c < n_chunks; c++) {
+            if (c + 1 < n_chunks) { stage(k_base, c + 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+            __syncthreads();
+            const uint8_t* tl = tile + (size_t)(c & 1) * ABT * ROWB;
+            const int r0 = warp * 8, tb = c * ABT + r0;          // eight positions per warp: one reduce8 batch
+            if (tb < n) {
+                float prod[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const __half* kr = reinterpret_cast<const __half*>(tl + (r0 + u) * ROWB);
+                    float acc = 0.f;
+#pragma unroll
+                    for (int i = 0; i < NI; i++) acc = fmaf(__half2float(kr[i * 32 + lane]), qreg[i], acc);
+                    prod[u] = acc;
+                }
+                float r = reduce8_lanes32(prod, lane);
+                const int u = reduce8_index(lane), t = tb + u;
+                if (t < n) {
+                    if (HD32 != HD) {               // ggml adds the tail beyond a multiple of 32 in f64
+                        const __half* kr = reinterpret_cast<const __half*>(tl + (r0 + u) * ROWB);
+                        double sumf = (double)r;
+                        for (int d = HD32; d < HD; d++) sumf += (double)__fmul_rn(__half2float(kr[d]), qs[d]);
+                        r = (float)sumf;
+                    }
+                    if ((lane & 3) == 0) sc[t] = __fmul_rn(r, a.scale);
+                }
+            }
+            __syncthreads();          // the chunk buffer is free again; after the last chunk: all scores are in place
+        }
+    }
+    // ---- 2. soft-max (ggml soft_max: one max, exp, f64 sum, scale by 1/sum; probabilities to f16) ----
+    {
+        float lmax = -INFINITY;
+        for (int t = tid; t < n; t += NT) lmax = fmaxf(lmax, sc[t]);
+        lmax = warp_max(lmax);
+        if (lane == 0) red[warp] = lmax;
+        __syncthreads();
+        float M = red[0];
+#pragma unroll
+        for (int w = 1; w < NWARP; w++) M = fmaxf(M, red[w]);
+        double lsum = 0.0;
+        for (int t = tid; t < n; t += NT) {
+            const float e = (float)exp((double)__fsub_rn(sc[t], M));
+            sc[t] = e;
+            lsum += (double)e;
+        }
+        lsum = warp_sum_d(lsum);
+        if (lane == 0) redd[warp] = lsum;
+        __syncthreads();
+        double S = 0;
+#pragma unroll
+        for (int w = 0; w < NWARP; w++) S += redd[w];
+        const float inv = (float)(1.0 / S);
+        for (int t = tid; t < n; t += NT) sc[t] = __half2float(__float2half_rn(__fmul_rn(sc[t], inv)));
+        __syncthreads();
+    }
+    // ---- 3. P.V: warp w owns dims [16w, 16w+16); lane L owns the positions L mod 32, one FMA chain per dim ----
+    {
+        const __half* const v_base = a.v_base + (size_t)kvh * HD;
+        const int d0 = 16 * warp;
+        const bool active = d0 < HD;
+        float acc[2][8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[0][j] = acc[1][j] = 0.f;
+        stage(v_base, 0);
+        for (int c = 0; c < n_chunks; c++) {
+            if (c + 1 < n_chunks) { stage(v_base, c + 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+            __syncthreads();
+            if (active) {
+                const uint8_t* tl = tile + (size_t)(c & 1) * ABT * ROWB + d0 * 2;
+#pragma unroll
+                for (int u = 0; u < ABT / 32; u++) {
+                    const int r = lane + 32 * u, t = c * ABT + r;
+                    if (t < n) {
+                        const float p = sc[t];
+                        const uint4 v0 = *reinterpret_cast<const uint4*>(tl + r * ROWB), v1 = *reinterpret_cast<const uint4*>(tl + r * ROWB + 16);
+                        const __half2* h0 = reinterpret_cast<const __half2*>(&v0);
+                        const __half2* h1 = reinterpret_cast<const __half2*>(&v1);
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float2 f0 = __half22float2(h0[j]), f1 = __half22float2(h1[j]);
+                            acc[0][2 * j] = fmaf(f0.x, p, acc[0][2 * j]); acc[0][2 * j + 1] = fmaf(f0.y, p, acc[0][2 * j + 1]);
+                            acc[1][2 * j] = fmaf(f1.x, p, acc[1][2 * j]); acc[1][2 * j + 1] = fmaf(f1.y, p, acc[1][2 * j + 1]);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (active) {
+            float* outh = a.out + (size_t)h * HD + d0;
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const float r = reduce8_lanes32(acc[half], lane);
+                if ((lane & 3) == 0) outh[8 * half + reduce8_index(lane)] = r;
+            }
+        }
+    }
+}
+
+template <int HD>
+int launch_batch_staged(const AttnArgs* d_args, const AttnArgs& a, int B, cudaStream_t st) {
+    const int maxc = (a.max_ctx + 3) / 4 * 4;
+    const size_t smem = (size_t)2 * maxc * 4 + (size_t)HD * 4 + 8 * 4 + 8 * 8 + (size_t)2 * ABT * (HD * 2 + 16);
+    auto kern = attn_batch_staged_kernel<HD>;
+    static PerDeviceSmem configured;
+    if (smem > 48 * 1024 && configured.raise(smem)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.n_head, B, 1);
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, d_args, maxc));
+    return B2_OK;
+}
+
 template <int GRP, int HD>
 int launch_grp(const AttnArgs& a, const AttnCfg& c, size_t smem, cudaStream_t st, bool pdl) {
     auto kern = attn_decode_kernel<GRP, HD>;
@@ -136,6 +310,13 @@ int attn_decode_launch(const AttnArgs& a, cudaStream_t st, bool pdl, int cluster
 int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& a, int B, cudaStream_t st) {
     if (a.max_ctx <= 0 || B < 1) B2_FAIL(B2_ERR_ARG, "attn: bad batch arguments");
     if (a.n_head_kv <= 0 || a.n_head % a.n_head_kv) B2_FAIL(B2_ERR_ARG, "attn: n_head %d not a multiple of n_head_kv %d", a.n_head, a.n_head_kv);
+    // many (column, head) pairs: the bandwidth-organised kernel; few: the latency-organised cluster kernel
+    const size_t staged_smem = (size_t)2 * ((a.max_ctx + 3) / 4 * 4) * 4 + (size_t)2 * ABT * (a.head_dim * 2 + 16) + 1024;
+    if ((size_t)B * a.n_head >= 128 && a.head_dim % 16 == 0 && a.head_dim <= 128 && staged_smem <= 100 * 1024 && !getenv("B2_ATTN_CLUSTER_ONLY")) {
+        if (a.head_dim == 64) return launch_batch_staged<64>(d_args, a, B, st);
+        if (a.head_dim == 80) return launch_batch_staged<80>(d_args, a, B, st);
+        if (a.head_dim == 128) return launch_batch_staged<128>(d_args, a, B, st);
+    }
     const int grp = a.n_head / a.n_head_kv;
     AttnCfg c;
     int cluster = 1;      // the columns already spread the work: only small batches split a head over CTAs
