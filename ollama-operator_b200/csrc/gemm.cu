@@ -73,7 +73,9 @@ __device__ __forceinline__ float half_of(uint32_t packed, int hi) {
     return __half2float(__ushort_as_half((unsigned short)(hi ? packed >> 16 : packed & 0xFFFFu)));
 }
 
-template <int NT>     // NT = 8-column MMA tiles (columns padded to 8 * NT)
+// NT = 8-column MMA tiles (columns padded to 8 * NT); SPLIT: every CTA has so few units (row tiles x NT <= 8)
+// that two warps share one, each taking one half of every K chunk
+template <int NT, bool SPLIT>
 __global__ void __launch_bounds__((GB_WARPS + 1) * 32, 1)
 gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const int rows, const int nbk, const int B, const GemvArgs* __restrict__ colargs,
                  const int* __restrict__ col_pos, const int* __restrict__ col_pt, const int pt_stride) {
@@ -160,7 +162,7 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
     uint32_t it = 0;
     for (int grp = 0; grp < n_grp; grp++) {
         const int gt0 = t0 + grp * per, n_rt = min(per, t1 - gt0), tot = n_rt * NT;
-        const int KS = NT <= 2 && 2 * tot <= GB_WARPS ? 2 : 1;      // (compiled out for wide batches: their units keep every warp busy)
+        constexpr int KS = SPLIT ? 2 : 1;
         double acc[GB_MAXI][4];
 #pragma unroll
         for (int m = 0; m < GB_MAXI; m++)
@@ -257,10 +259,10 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
     }
 }
 
-template <int NT>
+template <int NT, bool SPLIT>
 int gemm_launch_t(const GemmMaps& maps, const Q8Cols& x, int rows, int nbk, int B, const GemvArgs* colargs, const int* pos, const int* pt, int pt_stride, int grid,
                   cudaStream_t st) {
-    auto kern = gemm_w4a8_kernel<NT>;
+    auto kern = gemm_w4a8_kernel<NT, SPLIT>;
     static PerDeviceSmem configured;
     if (configured.raise(GB_SMEM)) B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GB_SMEM));
     cudaLaunchConfig_t cfg = {};
@@ -324,12 +326,20 @@ int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B
     const int T = (int)((W.rows + 15) / 16);
     const int grid = std::min(T, sms > 0 ? sms : 148);
     const int nt = (B + 7) / 8, rows = (int)W.rows, nbk = (int)(W.k / 32);
+    const int max_rt = (T + grid - 1) / grid;                 // row tiles of the busiest CTA
+    const bool split = max_rt <= GB_RTMAX && 2 * max_rt * nt <= GB_WARPS;
+#define B2_GEMM_CASE(N) \
+    case N: return split ? gemm_launch_t<N, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st) \
+                         : gemm_launch_t<N, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st)
     switch (nt) {
-    case 1: return gemm_launch_t<1>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st);
-    case 2: return gemm_launch_t<2>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st);
-    case 3: return gemm_launch_t<3>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st);
-    default: return gemm_launch_t<4>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st);
+        B2_GEMM_CASE(1);
+        B2_GEMM_CASE(2);
+        B2_GEMM_CASE(3);
+    default: break;
     }
+    return split ? gemm_launch_t<4, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st)
+                 : gemm_launch_t<4, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st);
+#undef B2_GEMM_CASE
 }
 
 }  // namespace b2
