@@ -92,11 +92,6 @@ int launch_grp_batch(const AttnArgs* d_args, int n_head_kv, int B, const AttnCfg
 // order through reduce8_lanes32 (tail dims in f64), one max, exp from f64, f64 sum, f16 probabilities, P.V as one
 // f32 FMA chain per (position mod 32, dim) in position order.  Same bits.
 constexpr int ABT = 64;                       // positions per chunk
-__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int HD>
 __global__ void __launch_bounds__(256) attn_batch_staged_kernel(const AttnArgs* __restrict__ args, const int maxc) {
