@@ -203,7 +203,6 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     use_mega = !(flags & B2_LOAD_NO_MEGA) && !getenv("B2_NO_MEGA");
     use_batch = !(flags & B2_LOAD_NO_BATCH) && !getenv("B2_NO_BATCH");
     tp_skip_reduce = getenv("B2_TP_SKIP_REDUCE") != nullptr;      // timing experiment only: results are wrong
-    if (tp_size > 1) use_batch = false;      // prompts are walked token by token under tensor parallelism
 
     const int E = hp.n_embd, hd = hp.head_dim, nq_full = hp.n_head * hd, nkv_full = hp.n_head_kv * hd, F_full = hp.n_ff, V = hp.n_vocab;
     const int nq = n_head_l * hd, nkv = n_head_kv_l * hd, F = n_ff_l;       // this shard's part
@@ -396,8 +395,10 @@ int Model::finish_load() {
     return B2_OK;
 }
 
+// Exchange buffers of this shard, in one allocation: [2][E] partial sums of a single-token step,
+// flags, epoch and ticket, then [2][BATCH_MAX][E] partial sums of a batched step.
 int Model::tp_alloc() {
-    const size_t part_bytes = (size_t)hp.n_embd * sizeof(double), total = 2 * part_bytes + 256 + 256;
+    const size_t part_bytes = (size_t)hp.n_embd * sizeof(double), total = 2 * part_bytes + 512 + 2 * BATCH_MAX * part_bytes;
     B2_CUDA(cudaMalloc(&tp_mem, total));
     B2_CUDA(cudaMemset(tp_mem, 0, total));
     return B2_OK;
@@ -424,6 +425,13 @@ int Model::tp_connect(Model* const* shards) {
     }
     tp.epoch = (unsigned*)((uint8_t*)tp_mem + 2 * part_bytes + 256);
     tp.ticket = tp.epoch + 1;
+    // batched steps: same flags and epoch sequence (every shard runs the same schedule), their own partial-sum buffers
+    tpb = tp;
+    for (int d = 0; d < tp_size; d++) {
+        uint8_t* b = (uint8_t*)shards[d]->tp_mem + 2 * part_bytes + 512;
+        tpb.part[0][d] = (double*)b;
+        tpb.part[1][d] = (double*)(b + BATCH_MAX * part_bytes);
+    }
     return finish_load();
 }
 

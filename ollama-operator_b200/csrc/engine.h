@@ -84,7 +84,7 @@ struct Model {
     HParams hp;                       // the whole model's hyper-parameters
     int tp_rank = 0, tp_size = 1;     // this shard of a tensor-parallel group (one shard per GPU)
     int n_head_l = 0, n_head_kv_l = 0, n_ff_l = 0;     // heads / FFN rows held by this shard
-    TpPeers tp;                       // peer-mapped partial-sum buffers and flags (tp_size > 1)
+    TpPeers tp, tpb;                  // peer-mapped partial-sum buffers and flags (tp_size > 1): single-token steps, batched steps
     void* tp_mem = nullptr;
     int device = 0;
     bool tp_skip_reduce = false;

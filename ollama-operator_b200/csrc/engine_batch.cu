@@ -25,7 +25,7 @@ static inline size_t align_up_b(size_t v, size_t a) { return (v + a - 1) / a * a
 int Model::setup_batch() {
     bt.ok = false;
     if (slots.empty()) return B2_OK;
-    const int E = hp.n_embd, hd = hp.head_dim, nq = hp.n_head * hd, F = hp.n_ff, V = hp.n_vocab;
+    const int E = hp.n_embd, hd = hp.head_dim, nq = n_head_l * hd, F = n_ff_l, V = hp.n_vocab;      // this shard's heads and FFN rows
     int64_t k_max = 0;
     for (const StepOp& op : slots[0].ops)
         if (op.kind == 0) {
@@ -70,6 +70,7 @@ int Model::setup_batch() {
             if (s0.ops[i].kind == 0) {
                 GemvArgs g = s0.ops[i].g;
                 g.x = rebind(g.x, c); g.y = rebind(g.y, c); g.y2 = rebind(g.y2, c);
+                if (s0.ops[i].tp_buf >= 0) g.y64 = tpb.part[s0.ops[i].tp_buf][tp_rank] + (size_t)c * E;      // K-split projection: per-column partial sums
                 g.kv.page_table = bt.d_pt + (size_t)c * pages_per_seq;
                 g.kv.pos = bt.d_pos + c;
                 ca[i * BATCH_MAX + c] = g;
@@ -129,11 +130,14 @@ int Model::batch_step(int B, const int* col_slot, const int* col_pos, const int3
             const bool reuse = i > 0 && bt.ops[i - 1].kind == 0 && bt.ops[i - 1].g.x == g.x && bt.ops[i - 1].g.pro == g.pro &&
                                bt.ops[i - 1].g.gain == g.gain && bt.ops[i - 1].g.W.k == g.W.k && g.epi == EPI_QKV_ROPE;
             if (!reuse) {
-                B2_TRY(quant_cols_launch(g.x, g.x == bt.x || g.x == bt.att2 ? E : g.x == bt.h ? hp.n_ff : hp.n_head * hp.head_dim, g.W.k, B, g.pro, g.gain,
+                B2_TRY(quant_cols_launch(g.x, g.x == bt.x || g.x == bt.att2 ? E : g.x == bt.h ? n_ff_l : n_head_l * hp.head_dim, g.W.k, B, g.pro, g.gain,
                                          g.nbias, g.eps, bt.q8, stream));
                 nl++;
             }
-            B2_TRY(gemm_w4a8_launch(g.W, bt.maps[i], bt.q8, B, bt.d_colargs + i * BATCH_MAX, bt.d_pos, bt.d_pt, pages_per_seq, stream)); nl++;
+            B2_TRY(gemm_w4a8_launch(g.W, bt.maps[i], bt.q8, B, bt.d_colargs + i * BATCH_MAX, bt.d_pos, bt.d_pt, pages_per_seq, stream, op.tp_buf >= 0)); nl++;
+            if (op.tp_buf >= 0) {      // all columns at once: x[c] += sum over the shards of their partial sums
+                B2_TRY(tp_allreduce_residual_launch(tpb, op.tp_buf, bt.x, B * E, stream, true)); nl++;
+            }
         } else {
             B2_TRY(attn_decode_batch_launch(bt.d_attargs + i * BATCH_MAX, op.a, B, stream)); nl++;
         }

@@ -159,6 +159,7 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
     // units (small batches, narrow matrices) two warps share a unit, each taking one half of every K chunk;
     // their f64 partial sums meet in shared memory, in a fixed order.
     const int g = lane >> 2, t = lane & 3;
+    const bool partial = colargs[0].epi == EPI_PARTIAL;      // tensor-parallel K slice: the f64 sums leave unrounded (same for every column)
     uint32_t it = 0;
     for (int grp = 0; grp < n_grp; grp++) {
         const int gt0 = t0 + grp * per, n_rt = min(per, t1 - gt0), tot = n_rt * NT;
@@ -225,9 +226,15 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
                 const int unit = warp + GB_WARPS * m;
                 if (unit < tot) {
                     const int rt = unit / NT, j = unit - rt * NT;
-                    float* o = outb + (rt * 16 + g) * GB_OUT_STRIDE + 8 * j + 2 * t;
-                    o[0] = (float)acc[m][0]; o[1] = (float)acc[m][1];
-                    o[8 * GB_OUT_STRIDE] = (float)acc[m][2]; o[8 * GB_OUT_STRIDE + 1] = (float)acc[m][3];
+                    if (partial) {          // [row][32] doubles (the host keeps such matrices to <= 5 row tiles per CTA)
+                        double* o = outd + (rt * 16 + g) * BATCH_MAX + 8 * j + 2 * t;
+                        o[0] = acc[m][0]; o[1] = acc[m][1];
+                        o[8 * BATCH_MAX] = acc[m][2]; o[8 * BATCH_MAX + 1] = acc[m][3];
+                    } else {
+                        float* o = outb + (rt * 16 + g) * GB_OUT_STRIDE + 8 * j + 2 * t;
+                        o[0] = (float)acc[m][0]; o[1] = (float)acc[m][1];
+                        o[8 * GB_OUT_STRIDE] = (float)acc[m][2]; o[8 * GB_OUT_STRIDE + 1] = (float)acc[m][3];
+                    }
                 }
             }
         }
@@ -237,22 +244,32 @@ gemm_w4a8_kernel(const __grid_constant__ GemmMaps maps, const Q8Cols xin, const 
             const int p = i / B, c = i - p * B;
             const int64_t r0 = (int64_t)gt0 * 16 + 2 * p;
             if (r0 < rows) {
-                float v0, v1;
+                float v0 = 0.f, v1 = 0.f;
+                double s0 = 0.0, s1 = 0.0;
                 if (KS == 2) {
                     // rows 2p, 2p+1 of the group, column c: unit, lane and register of the MMA accumulator layout
                     const int rl = 2 * p, unit = (rl >> 4) * NT + (c >> 3), ln = (rl & 7) * 4 + ((c & 7) >> 1), q = ((rl & 8) ? 2 : 0) + (c & 1);
                     const double* p0 = outd + (unit * 4 + q) * 32 + ln;
                     const double* p1 = outd + ((tot + unit) * 4 + q) * 32 + ln;
-                    v0 = (float)(p0[0] + p1[0]);
-                    v1 = (float)(p0[4] + p1[4]);            // row + 1: the next lane group (g + 1), same column
+                    s0 = p0[0] + p1[0];
+                    s1 = p0[4] + p1[4];                     // row + 1: the next lane group (g + 1), same column
+                    v0 = (float)s0; v1 = (float)s1;
+                } else if (partial) {
+                    s0 = outd[(2 * p) * BATCH_MAX + c];
+                    s1 = outd[(2 * p + 1) * BATCH_MAX + c];
                 } else {
                     v0 = outb[(2 * p) * GB_OUT_STRIDE + c];
                     v1 = outb[(2 * p + 1) * GB_OUT_STRIDE + c];
                 }
-                unsigned long long best = 0ull;
                 const GemvArgs& a = colargs[c];
-                epilogue_pair(a, a.epi_row0 + r0, v0, v1, best, col_pos[c], col_pt + (size_t)c * pt_stride);
-                if (a.epi == EPI_LOGITS && best != 0ull) atomicMax(a.argmax_key, best);
+                if (partial) {
+                    a.y64[a.epi_row0 + r0] = s0;
+                    a.y64[a.epi_row0 + r0 + 1] = s1;
+                } else {
+                    unsigned long long best = 0ull;
+                    epilogue_pair(a, a.epi_row0 + r0, v0, v1, best, col_pos[c], col_pt + (size_t)c * pt_stride);
+                    if (a.epi == EPI_LOGITS && best != 0ull) atomicMax(a.argmax_key, best);
+                }
             }
         }
         named_bar_sync(1, GB_NTC);
@@ -316,7 +333,7 @@ int gemm_make_maps(const QMat& W, GemmMaps* out) {
 }
 
 int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride,
-                     cudaStream_t st) {
+                     cudaStream_t st, bool partial_out) {
     if (!gemm_supported(W)) B2_FAIL(B2_ERR_UNSUPPORTED, "gemm: type %d shape %lld x %lld has no batched kernel", W.type, (long long)W.rows, (long long)W.k);
     if (B < 1 || B > BATCH_MAX) B2_FAIL(B2_ERR_ARG, "gemm: %d columns (1..%d)", B, BATCH_MAX);
     if (W.k > x.k_cap) B2_FAIL(B2_ERR_ARG, "gemm: K=%lld beyond the activation buffer (%lld)", (long long)W.k, (long long)x.k_cap);
@@ -327,6 +344,8 @@ int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B
     const int grid = std::min(T, sms > 0 ? sms : 148);
     const int nt = (B + 7) / 8, rows = (int)W.rows, nbk = (int)(W.k / 32);
     const int max_rt = (T + grid - 1) / grid;                 // row tiles of the busiest CTA
+    static_assert(5 * 16 * BATCH_MAX * 8 <= GB_OUT_BYTES, "f64 output staging of a K-split matrix");
+    if (partial_out && max_rt > 5) B2_FAIL(B2_ERR_UNSUPPORTED, "gemm: a K-split matrix with %d rows leaves %d row tiles per CTA (at most 5)", rows, max_rt);
     const bool split = max_rt <= GB_RTMAX && 2 * max_rt * nt <= GB_WARPS;
 #define B2_GEMM_CASE(N) \
     case N: return split ? gemm_launch_t<N, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, grid, st) \

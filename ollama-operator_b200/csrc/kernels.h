@@ -188,7 +188,7 @@ int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pr
 bool gemm_supported(const QMat& W);
 int gemm_make_maps(const QMat& W, GemmMaps* out);
 int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride,
-                     cudaStream_t st);
+                     cudaStream_t st, bool partial_out = false);      // partial_out: the columns' epilogue is EPI_PARTIAL
 // attention for B columns: d_args[c] describes column c (q, out, page table, position pointer)
 int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& shape, int B, cudaStream_t st);
 // next token of every column from its arg-max accumulator

@@ -28,13 +28,15 @@ def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp, f
     E = pkg.engine
     path = pkg.synth.cached_model(preset, model_dir)
     e1, en = E.Engine(0), E.Engine(list(range(tp)))
-    m1 = e1.load(path, max_batch=2, max_ctx=256)
-    mt = en.load(path, max_batch=2, max_ctx=256, tp_size=tp, flags=flags)
+    m1 = e1.load(path, max_batch=5, max_ctx=256)
+    mt = en.load(path, max_batch=5, max_ctx=256, tp_size=tp, flags=flags)
     assert mt.info.n_head == m1.info.n_head and mt.info.step_weight_bytes >= m1.info.step_weight_bytes
     toks = pkg.synth.prompt_tokens(21, m1.info.n_vocab, seed=5)
     s1, st = m1.seq_new(), mt.seq_new()
     l1, lt = m1.prefill(s1, toks), mt.prefill(st, toks)
     assert np.array_equal(_bits(l1), _bits(lt)), np.abs(l1 - lt).max()
+    if preset == "tiny-gqa8" and flags == 0:
+        assert mt.stats().last_steps == 1          # the 21-token prompt went through the batched kernels as one chunk, also under TP
     # against the oracle directly as well
     om = oracle.OracleModel(path, faithful=2)
     for t in toks:
@@ -56,4 +58,16 @@ def test_tensor_parallel_equals_single_gpu(pkg, oracle, model_dir, preset, tp, f
     assert s1b == stb
     more = pkg.synth.prompt_tokens(9, m1.info.n_vocab, seed=6)
     assert np.array_equal(_bits(m1.prefill(s1b, more)), _bits(mt.prefill(stb, more)))
+    # several sequences in one call: batched columns under tensor parallelism (where the shard shapes allow it)
+    q1, qt, tk = [s1, s1b], [st, stb], [3, 4]
+    for i in range(3):
+        a1, at = m1.seq_new(), mt.seq_new()
+        pr = pkg.synth.prompt_tokens(5 + 30 * i, m1.info.n_vocab, seed=20 + i)
+        assert np.array_equal(_bits(m1.prefill(a1, pr)), _bits(mt.prefill(at, pr)))
+        q1.append(a1); qt.append(at); tk.append(5 + i)
+    for _ in range(4):
+        n1, g1 = m1.decode(q1, tk, want_logits=True)
+        nt, gt = mt.decode(qt, tk, want_logits=True)
+        assert np.array_equal(_bits(g1), _bits(gt)) and np.array_equal(n1, nt)
+        tk = [int(x) for x in n1]
     mt.close(); m1.close(); en.close(); e1.close()

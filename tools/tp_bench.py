@@ -23,7 +23,7 @@ ref = None
 for tp in tps:
     eng = E.Engine(list(range(tp)))
     t0 = time.time()
-    m = eng.load(path, max_batch=1, max_ctx=ctx + steps + 72, tp_size=tp)
+    m = eng.load(path, max_batch=2 + int(os.environ.get("TP_BENCH_BATCH", "0")), max_ctx=max(ctx + steps + 72, 640), tp_size=tp)
     load_s = time.time() - t0
     info = m.info
     s = m.seq_new()
@@ -41,11 +41,25 @@ for tp in tps:
     for _ in range(32):
         last = int(m.decode([s], [last])[0])
     e2e_ms = (time.perf_counter() - t0) / 32 * 1e3
+    nb = int(os.environ.get("TP_BENCH_BATCH", "0"))
+    batch = None
+    if nb > 1:          # nb sequences decoded together (batched columns), each at the same synthetic context
+        seqs = []
+        for i in range(nb):
+            q = m.seq_new(); m.seq_assume(q, ctx - 16); m.prefill(q, p.synth.prompt_tokens(16, info.n_vocab, seed=50 + i)); seqs.append(q)
+        tk = [1] * nb
+        for _ in range(3): tk = [int(x) for x in m.decode(seqs, tk)]
+        g = []
+        for _ in range(8):
+            tk = [int(x) for x in m.decode(seqs, tk)]; g.append(m.stats().gpu_ms)
+        batch = {"n_seq": nb, "ms_per_step": round(float(np.median(g)), 3), "tok_s": round(nb / float(np.median(g)) * 1e3, 1), "tokens": tk[:4]}
+        t0 = time.perf_counter(); q = m.seq_new(); m.prefill(q, p.synth.prompt_tokens(512, info.n_vocab, seed=77))
+        batch["prefill512_ms"] = round(m.stats().gpu_ms, 1)
     step_bytes = info.step_weight_bytes + (ctx + 8 + steps // 2) * info.kv_bytes_per_token
     frac = step_bytes / tp / (ms * 1e-3) / 1e9 / peak
     same = None if ref is None else bool(np.array_equal(ref, toks))
     if ref is None: ref = toks
     print(json.dumps({"model": preset, "tp": tp, "ctx": ctx, "steps": steps, "ms_per_step": round(ms, 4), "tok_s": round(1e3 / ms, 1),
                       "e2e_tok_s": round(1e3 / e2e_ms, 1), "per_gpu_bytes_per_step": int(step_bytes / tp), "per_gpu_hbm_frac": round(frac, 4),
-                      "tokens_equal_first_run": same, "load_s": round(load_s, 1), "prefill_s": round(pre_s, 1)}), flush=True)
+                      "tokens_equal_first_run": same, "load_s": round(load_s, 1), "prefill_s": round(pre_s, 1), "batch": batch}), flush=True)
     m.close(); eng.close()
