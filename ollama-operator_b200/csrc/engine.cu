@@ -294,29 +294,41 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
             B2_TRY(upload_quant(P.gate.t, F, E, L.w_up, 0, 2, (int64_t)tp_rank * F));
             B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 1, 2, (int64_t)tp_rank * F));
         } else {
+            // attention and MLP of a phi-2 block read the same normed input: when the tensor types agree,
+            // ffn_up's rows follow q|k|v in ONE matrix (one stage, one prologue, one barrier less per layer)
+            const int64_t nqkv = nq + 2 * nkv;
+            L.fused_up = P.qkv.t->type == P.up.t->type && !getenv("B2_NO_FUSED_UP");
             QkvSeg seg;
             seg.row0 = 0;
-            B2_TRY(qmat_alloc(arena, seg.W, P.qkv.t->type, nq + 2 * nkv, E));
-            B2_TRY(upload_rows_headwise(P.qkv.t, (nq + 2 * nkv) / hd, E, seg.W, 0, 0));
+            B2_TRY(qmat_alloc(arena, seg.W, P.qkv.t->type, nqkv + (L.fused_up ? F : 0), E));
+            B2_TRY(upload_rows_headwise(P.qkv.t, nqkv / hd, E, seg.W, 0, 0));
+            if (L.fused_up) B2_TRY(upload_quant(P.up.t, F, E, seg.W, nqkv, 1, 0));
             L.qkv.push_back(seg);
             // bias rows follow the same permutation
             const GgufTensor* tb = f.find(p + "attn_qkv.bias");
-            if (tb) {
-                if (tb->type != T_F32 || tb->ne.empty() || tb->ne[0] != nq + 2 * nkv) B2_FAIL(B2_ERR_FORMAT, "gguf: %sattn_qkv.bias mis-shaped", p.c_str());
-                std::vector<float> b((size_t)nq + 2 * nkv);
-                const float* src = (const float*)tb->data;
-                for (int64_t h = 0; h < (nq + 2 * nkv) / hd; h++)
-                    for (int e = 0; e < hd; e++) {
-                        const int dsti = e < hp.n_rot / 2 ? 2 * e : e < hp.n_rot ? 2 * (e - hp.n_rot / 2) + 1 : e;
-                        b[h * hd + dsti] = src[h * hd + e];
-                    }
+            const GgufTensor* tub = f.find(p + "ffn_up.bias");
+            if (tub && (tub->type != T_F32 || tub->ne.empty() || tub->ne[0] != F)) B2_FAIL(B2_ERR_FORMAT, "gguf: %sffn_up.bias mis-shaped", p.c_str());
+            if (tb || (L.fused_up && tub)) {
+                if (tb && (tb->type != T_F32 || tb->ne.empty() || tb->ne[0] != nqkv)) B2_FAIL(B2_ERR_FORMAT, "gguf: %sattn_qkv.bias mis-shaped", p.c_str());
+                std::vector<float> b((size_t)nqkv + (L.fused_up ? F : 0), 0.f);
+                if (tb) {
+                    const float* src = (const float*)tb->data;
+                    for (int64_t h = 0; h < nqkv / hd; h++)
+                        for (int e = 0; e < hd; e++) {
+                            const int dsti = e < hp.n_rot / 2 ? 2 * e : e < hp.n_rot ? 2 * (e - hp.n_rot / 2) + 1 : e;
+                            b[h * hd + dsti] = src[h * hd + e];
+                        }
+                }
+                if (L.fused_up && tub) memcpy(b.data() + nqkv, tub->data, (size_t)F * 4);
                 L.b_qkv = (float*)arena.take(b.size() * 4);
                 if (!L.b_qkv) B2_FAIL(B2_ERR_NOMEM, "weight arena exhausted");
                 B2_CUDA(cudaMemcpy(L.b_qkv, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
             }
-            B2_TRY(qmat_alloc(arena, L.w_up, P.up.t->type, F, E));
-            B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 0, 1, 0));
-            B2_TRY(upload_f32(f, p + "ffn_up.bias", F, &L.b_up, true));
+            if (!L.fused_up) {
+                B2_TRY(qmat_alloc(arena, L.w_up, P.up.t->type, F, E));
+                B2_TRY(upload_quant(P.up.t, F, E, L.w_up, 0, 1, 0));
+                B2_TRY(upload_f32(f, p + "ffn_up.bias", F, &L.b_up, true));
+            }
             B2_TRY(upload_f32(f, p + "ffn_down.bias", E, &L.b_down, true));
             B2_TRY(upload_f32(f, p + "attn_output.bias", E, &L.b_o, true));
         }
@@ -330,7 +342,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
             B2_TRY(upload_quant_kslice(P.down.t, E, F_full, (int64_t)tp_rank * F, F, L.w_down));
         }
         for (auto& s : L.qkv) step_weight_bytes += gemv_weight_bytes(s.W);
-        step_weight_bytes += gemv_weight_bytes(L.w_o) + gemv_weight_bytes(L.w_up) + gemv_weight_bytes(L.w_down) + (size_t)2 * E * 4;
+        step_weight_bytes += gemv_weight_bytes(L.w_o) + (L.fused_up ? 0 : gemv_weight_bytes(L.w_up)) + gemv_weight_bytes(L.w_down) + (size_t)2 * E * 4;
     }
     weight_bytes = arena.used;
     cudaFree(staging);
@@ -511,6 +523,7 @@ void Model::build_ops(Slot& s) {
             a.W = seg.W; a.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; a.epi = EPI_QKV_ROPE;
             a.x = s.x; a.gain = L.attn_norm; a.nbias = L.attn_norm_b; a.eps = hp.norm_eps;
             a.bias = L.b_qkv; a.y = s.q; a.epi_row0 = seg.row0;
+            if (L.fused_up) { a.epi = EPI_QKV_ROPE_GELU; a.y3 = s.h; }
             a.n_q = nq; a.n_kv = nkv; a.head_dim = hd; a.n_rot = hp.n_rot; a.rope_neox = neox ? 1 : 0;
             a.q_scale = hp.arch == 1 ? 1.0f / sqrtf((float)hd) : 1.0f;
             a.rope_cs = rope_table;
@@ -543,7 +556,9 @@ void Model::build_ops(Slot& s) {
             u.g.eps = hp.norm_eps; u.g.bias = L.b_up; u.g.y = s.h;
             d.g.W = L.w_down; d.g.pro = PRO_PLAIN; d.g.epi = EPI_RESIDUAL2; d.g.x = s.h; d.g.bias = L.b_down; d.g.y = s.x; d.g.y2 = s.att2;
         }
-        s.ops.push_back(o); s.ops.push_back(u); s.ops.push_back(d);
+        s.ops.push_back(o);
+        if (!L.fused_up) s.ops.push_back(u);
+        s.ops.push_back(d);
     }
 }
 

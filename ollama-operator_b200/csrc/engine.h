@@ -34,6 +34,7 @@ struct LayerW {
     QMat w_o, w_up, w_down;        // llama: w_up holds gate and up interleaved row by row
     float *attn_norm = nullptr, *attn_norm_b = nullptr, *ffn_norm = nullptr;
     float *b_qkv = nullptr, *b_o = nullptr, *b_up = nullptr, *b_down = nullptr;
+    bool fused_up = false;         // phi-2: ffn_up rows follow q|k|v in qkv[0].W (one stage for the parallel block's shared input), b_qkv covers both
 };
 
 struct StepOp { int kind = 0; int cls = 0; GemvArgs g; AttnArgs a; int tp_buf = -1; };     // kind 0 = GEMV, 1 = attention; tp_buf >= 0: all-reduce follows

@@ -69,7 +69,7 @@ int Model::setup_batch() {
         for (int c = 0; c < BATCH_MAX; c++) {
             if (s0.ops[i].kind == 0) {
                 GemvArgs g = s0.ops[i].g;
-                g.x = rebind(g.x, c); g.y = rebind(g.y, c); g.y2 = rebind(g.y2, c);
+                g.x = rebind(g.x, c); g.y = rebind(g.y, c); g.y2 = rebind(g.y2, c); g.y3 = rebind(g.y3, c);
                 if (s0.ops[i].tp_buf >= 0) g.y64 = tpb.part[s0.ops[i].tp_buf][tp_rank] + (size_t)c * E;      // K-split projection: per-column partial sums
                 g.kv.page_table = bt.d_pt + (size_t)c * pages_per_seq;
                 g.kv.pos = bt.d_pos + c;

@@ -430,7 +430,13 @@ __device__ __forceinline__ float gelu_f16_table(float v) {
 static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best, int pos_value = -1,
                                      const int* page_table_override = nullptr) {
     if (a.bias) { v0 = __fadd_rn(v0, a.bias[r0]); v1 = __fadd_rn(v1, a.bias[r0 + 1]); }
-    switch (a.epi) {
+    int epi = a.epi;
+    if (epi == EPI_QKV_ROPE_GELU) {
+        const int64_t nqkv = (int64_t)a.n_q + 2 * a.n_kv;
+        if (r0 >= nqkv) { a.y3[r0 - nqkv] = gelu_f16_table(v0); a.y3[r0 - nqkv + 1] = gelu_f16_table(v1); return; }
+        epi = EPI_QKV_ROPE;
+    }
+    switch (epi) {
     case EPI_STORE: a.y[r0] = v0; a.y[r0 + 1] = v1; break;
     case EPI_RESIDUAL: a.y[r0] = __fadd_rn(a.y[r0], v0); a.y[r0 + 1] = __fadd_rn(a.y[r0 + 1], v1); break;
     case EPI_RESIDUAL2:

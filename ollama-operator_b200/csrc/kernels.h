@@ -24,7 +24,9 @@ enum GemvEpi : int {
     EPI_LOGITS = 4,      // y[r] = v and a running arg-max into *argmax_key
     EPI_GELU = 5,        // y[r] = gelu(v)
     EPI_RESIDUAL2 = 6,   // y[r] = (v + y2[r]) + y[r]   (phi-2 parallel block: ffn + attn + x)
-    EPI_PARTIAL = 7,     // y64[r] = the f64 sum, unrounded (tensor-parallel K slice; per-matrix GEMV only)
+    EPI_PARTIAL = 7,     // y64[r] = the f64 sum, unrounded (tensor-parallel K slice)
+    EPI_QKV_ROPE_GELU = 8,   // phi-2 parallel block: rows [q | k | v | ffn_up] share the normed input; the first
+                             // n_q + 2 n_kv rows as EPI_QKV_ROPE, the rest as GELU into y3
 };
 
 struct KvDesc {                 // where the new token's K and V go (one layer, one sequence slot)
@@ -46,6 +48,7 @@ struct GemvArgs {
     float* y = nullptr;
     const float* y2 = nullptr;
     double* y64 = nullptr;         // EPI_PARTIAL
+    float* y3 = nullptr;           // EPI_QKV_ROPE_GELU: the FFN hidden vector
     int64_t epi_row0 = 0;          // added to the matrix row before the epilogue (split QKV matrices)
     // EPI_QKV_ROPE
     int n_q = 0, n_kv = 0, head_dim = 0, n_rot = 0, rope_neox = 0;

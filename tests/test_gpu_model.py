@@ -158,3 +158,24 @@ def test_load_errors(pkg, eng, tmp_path):
     with pytest.raises(pkg.engine.B2Error) as e:
         eng.load(str(bad))
     assert e.value.code == -4
+
+
+def test_tensor_parallel_and_tooling_argument_errors(pkg, eng, model_dir):
+    E = pkg.engine
+    path = pkg.synth.cached_model("tiny-llama", model_dir)
+    with pytest.raises(E.B2Error) as e:          # one device bound, two asked for
+        eng.load(path, tp_size=2)
+    assert e.value.code == -1 and "tp_size" in str(e.value)
+    m = eng.load(path, max_batch=1, max_ctx=128)
+    s = m.seq_new()
+    m.prefill(s, pkg.synth.prompt_tokens(10, m.info.n_vocab))
+    with pytest.raises(E.B2Error):               # cannot "assume" fewer rows than the sequence holds
+        m.seq_assume(s, 5)
+    with pytest.raises(E.B2Error) as e:          # nor more than the cache can hold
+        m.seq_assume(s, 1000)
+    assert e.value.code == -6
+    m.seq_assume(s, 100)
+    assert m.seq_len(s) == 100
+    nxt = m.decode([s], [3])
+    assert 0 <= int(nxt[0]) < m.info.n_vocab and m.seq_len(s) == 101
+    m.close()
