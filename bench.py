@@ -262,7 +262,7 @@ def run_gpu(args):
     if prof_ms.get("persistent_layers", 0) > 0:
         k_ms = prof_ms["persistent_layers"]
         k_bytes = info.step_weight_bytes - head_bytes + m.seq_len(seq) * info.kv_bytes_per_token
-        k_name = f"mega_kernel<Q4_0> all {cfg.n_layer} layers of one decode step (weights + KV reads)"
+        k_name = f"mega_kernel<{'K-quants' if cfg.ftype == 'q4_k_m' else cfg.ftype.upper()}> all {cfg.n_layer} layers of one decode step (weights + KV reads)"
     else:
         k_ms = E.gemv_bench(body_type, rows_up, cfg.n_embd, iters=200)
         k_bytes = rows_up * cfg.n_embd * bpw
