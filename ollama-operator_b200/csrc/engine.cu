@@ -77,6 +77,7 @@ Model::~Model() {
     if (kv_v) cudaFree(kv_v);
     if (slot_mem) cudaFree(slot_mem);
     if (tp_mem) cudaFree(tp_mem);
+    if (pin_state) cudaFreeHost(pin_state);
     if (bt.mem) cudaFree(bt.mem);
     if (bt.h_stage) cudaFreeHost(bt.h_stage);
     if (bt.h_next) cudaFreeHost(bt.h_next);
@@ -370,6 +371,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
     B2_CUDA(cudaMemset(slot_mem, 0, slot_bytes * max_batch));
     slots.resize(max_batch);
+    B2_CUDA(cudaMallocHost(&pin_state, (size_t)2 * max_batch * sizeof(SeqState)));
     for (int i = 0; i < max_batch; i++) {
         uint8_t* b = (uint8_t*)slot_mem + slot_bytes * i;
         Slot& s = slots[i];
@@ -812,18 +814,22 @@ int Model::decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* 
         for (int i = 0; i < n_seq; i++) slots[seqs[i]].len += 1;
         return B2_OK;
     }
+    // the sequence state crosses the bus through pinned staging (pageable copies would each synchronise):
+    // everything of this call is queued, then ONE synchronisation
     for (int i = 0; i < n_seq; i++) {
         Slot& s = slots[seqs[i]];
-        SeqState st{};
+        SeqState& st = pin_state[2 * seqs[i]];
+        st = SeqState{};
         st.pos = s.len; st.cur_tok = last_tok[i];
         B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
         B2_TRY(run_steps(s, true, 1));
         if (logits) B2_CUDA(cudaMemcpyAsync(logits + (size_t)i * hp.n_vocab, s.logits, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
-        B2_CUDA(cudaMemcpyAsync(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost, stream));
+        B2_CUDA(cudaMemcpyAsync(&pin_state[2 * seqs[i] + 1], s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost, stream));
     }
     B2_TRY(end_call(nullptr));
     for (int i = 0; i < n_seq; i++) {
         Slot& s = slots[seqs[i]];
+        s.host = pin_state[2 * seqs[i] + 1];
         s.len += 1;
         if (next_tok) next_tok[i] = s.host.cur_tok;
     }

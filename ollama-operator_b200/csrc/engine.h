@@ -101,6 +101,7 @@ struct Model {
     size_t layer_kv_elems = 0;
     std::vector<int> free_pages;
     void* slot_mem = nullptr;
+    SeqState* pin_state = nullptr;     // pinned host staging: [slot][up, down]
     std::vector<Slot> slots;
     BatchCtx bt;
     int batch_min_seqs = 3;           // b2_decode switches to the batched kernels from this many sequences
