@@ -40,13 +40,17 @@ __global__ void batch_end_kernel(const unsigned long long* keys, int* next, int 
 
 // ---- quant_cols: one CTA per column; the GEMV prologue (same statistics, same quantiser as
 // prologue_q8_0 in gemv_dev.cuh) writing the chunk-major global layout of Q8Cols -------------------------
+constexpr int QC_SLICE = 1024;           // elements one CTA quantises: one 4-element chunk per thread, one global round trip
 __global__ void __launch_bounds__(256) quant_cols_kernel(GemvArgs a, int64_t x_stride, Q8Cols out) {
     __shared__ double dscratch[32];
     const int c = blockIdx.x, tid = threadIdx.x;
     a.x += (size_t)c * x_stride;
     pdl_trigger();       // the batched kernel that consumes these columns may start streaming its weights
     pdl_wait();          // the activations come from the preceding kernel, which may also still be reading the buffer we overwrite
+    // every CTA of a column computes the column's norm statistics (a streaming pass over K, identical in all of them),
+    // then quantises its own slice
     const ProStats st = prologue_stats(a, dscratch, tid, 256);
+    const int k0 = blockIdx.y * QC_SLICE, k1 = min((int)a.W.k, k0 + QC_SLICE);
     prologue_q8_0_each(a, st, tid, 256, [=](int blk, int o, uint32_t w, float d, int s8) {
         const int kc = blk / GEMM_KC, bl = blk % GEMM_KC;
         *reinterpret_cast<uint32_t*>(out.q + ((size_t)kc * BATCH_MAX + c) * GEMM_XCOL + (o < 16 ? 0 : GEMM_KC * 16) + bl * 16 + (o & 15)) = w;
@@ -54,7 +58,7 @@ __global__ void __launch_bounds__(256) quant_cols_kernel(GemvArgs a, int64_t x_s
             out.d[((size_t)kc * GEMM_KC + bl) * BATCH_MAX + c] = d;
             out.s8[((size_t)kc * GEMM_KC + bl) * BATCH_MAX + c] = -s8;        // the MMA accumulator starts from it
         }
-    });
+    }, k0, k1);
 }
 }  // namespace
 
@@ -75,7 +79,7 @@ int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pr
     GemvArgs a;
     a.W.k = K; a.pro = pro; a.x = x; a.gain = gain; a.nbias = nbias; a.eps = eps;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(B);
+    cfg.gridDim = dim3(B, (unsigned)((K + QC_SLICE - 1) / QC_SLICE));
     cfg.blockDim = dim3(256);
     cfg.stream = st;
     cudaLaunchAttribute at[1];

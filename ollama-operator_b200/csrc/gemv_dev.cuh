@@ -107,10 +107,10 @@ __device__ __forceinline__ uint32_t pack4(int a, int b, int c, int d) {
 // The quantiser proper: store(block, offset in block (multiple of 4), four packed int8, f16-rounded scale, 8*sum(q));
 // scale and sum are valid for offset 0 only.
 template <class Store>
-static __device__ __forceinline__ void prologue_q8_0_each(const GemvArgs& a, const ProStats& st, int tid, int ntc, Store store) {
-    const int K = (int)a.W.k;
+static __device__ __forceinline__ void prologue_q8_0_each(const GemvArgs& a, const ProStats& st, int tid, int ntc, Store store, int k0 = 0, int k1 = -1) {
+    const int K = k1 < 0 ? (int)a.W.k : k1;          // elements [k0, K): k0 and K multiples of 32
     const unsigned lane = tid & 31, gmask = 0xFFu << (lane & ~7u);
-    for (int i = tid * 4; i < K; i += ntc * 4) {
+    for (int i = k0 + tid * 4; i < K; i += ntc * 4) {
         const float4 v = prologue_vals(a, st, i);
         float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
         amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 1));
