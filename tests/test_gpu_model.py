@@ -179,3 +179,40 @@ def test_tensor_parallel_and_tooling_argument_errors(pkg, eng, model_dir):
     nxt = m.decode([s], [3])
     assert 0 <= int(nxt[0]) < m.info.n_vocab and m.seq_len(s) == 101
     m.close()
+
+
+def test_cache_edges_and_prefix_reuse(pkg, eng, model_dir):
+    """Empty prompts, a cache filled to its last row, truncation and re-evaluation of a suffix (prefix reuse)."""
+    E = pkg.engine
+    path = pkg.synth.cached_model("tiny-llama", model_dir)
+    m = eng.load(path, max_batch=1, max_ctx=64)
+    V = m.info.n_vocab
+    s = m.seq_new()
+    with pytest.raises(E.B2Error):
+        m.prefill(s, [])                                 # nothing to evaluate
+    toks = pkg.synth.prompt_tokens(64, V, seed=11)
+    full = m.prefill(s, toks)                            # exactly max_ctx tokens: the last cache row is used
+    assert m.seq_len(s) == 64
+    with pytest.raises(E.B2Error) as e:
+        m.decode([s], [1])                               # one more does not fit
+    assert e.value.code == -6
+    with pytest.raises(E.B2Error):
+        m.decode_greedy(s, 1, first_tok=1)
+    # drop the last 24 tokens and evaluate them again: same logits as the first time, bit for bit
+    m.seq_truncate(s, 40)
+    assert m.seq_len(s) == 40
+    again = m.prefill(s, toks[40:])
+    assert np.array_equal(again.view(np.uint32), full.view(np.uint32))
+    # and token by token through b2_decode
+    m.seq_truncate(s, 60)
+    lg = None
+    for t in toks[60:]:
+        _, lgs = m.decode([s], [int(t)], want_logits=True)
+        lg = lgs[0]
+    assert np.array_equal(lg.view(np.uint32), full.view(np.uint32))
+    with pytest.raises(E.B2Error):
+        m.seq_truncate(s, 65)
+    m.seq_free(s)
+    with pytest.raises(E.B2Error):
+        m.seq_len(s)
+    m.close()
