@@ -148,7 +148,7 @@ int Model::batch_step(int B, const int* col_slot, const int* col_pos, const int3
             h.W = w_head; h.pro = hp.arch == 0 ? PRO_RMSNORM : PRO_LAYERNORM; h.epi = EPI_LOGITS;
             h.x = bt.x + (size_t)c * E; h.gain = out_norm; h.nbias = out_norm_b; h.eps = hp.norm_eps; h.bias = head_b;
             h.y = bt.logits + (size_t)c * hp.n_vocab; h.argmax_key = bt.d_keys + c;
-            B2_TRY(gemv_launch(h, stream, false)); nl++;
+            B2_TRY(gemv_launch(h, stream, use_pdl)); nl++;      // consecutive head launches overlap their ring priming with the predecessor's tail
         }
     if (head_mask) { B2_TRY(batch_end_launch(bt.d_keys, bt.d_next, B, stream)); nl++; }
     launches += nl; last_launches += nl;
