@@ -66,7 +66,11 @@ bool read_value(Cursor& c, uint32_t t, GgufValue& v, int depth = 0) {
         const uint32_t et = c.get<uint32_t>();
         const uint64_t n = c.get<uint64_t>();
         v.arr_len = n;
-        if (const size_t es = scalar_size(et)) c.skip(n * es);
+        if (const size_t es = scalar_size(et)) {
+            uint64_t nbytes = 0;
+            if (__builtin_mul_overflow(n, (uint64_t)es, &nbytes)) { c.ok = false; return false; }
+            c.skip(nbytes);
+        }
         else if (et == 8) { for (uint64_t i = 0; i < n && c.ok; i++) c.str(); }
         else if (et == 9 && depth < 4) { GgufValue tmp; for (uint64_t i = 0; i < n && c.ok; i++) read_value(c, 9, tmp, depth + 1); }
         else return false;
@@ -125,15 +129,25 @@ int GgufFile::open(const char* path) {
     get_u64("general.alignment", &align);
     if (align == 0 || (align & (align - 1))) B2_FAIL(B2_ERR_FORMAT, "gguf: %s: bad alignment %llu", path, (unsigned long long)align);
     const size_t data_start = ((size_t)(c.p - map_) + align - 1) / align * align;
+    if (data_start > size_) B2_FAIL(B2_ERR_FORMAT, "gguf: %s: no tensor data section", path);
+    const uint64_t data_size = size_ - data_start;
     for (size_t i = 0; i < tensors_.size(); i++) {
         auto& t = tensors_[i];
-        int64_t n = 1;
-        for (int64_t d : t.ne) n *= d;
+        // element count with overflow checks: a zero or negative dimension, or a product that wraps, must not
+        // yield a small `bytes` that passes the range test below
+        uint64_t n = 1;
+        for (int64_t d : t.ne) {
+            if (d <= 0) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s: dimension %lld is not positive", t.name.c_str(), (long long)d);
+            if (__builtin_mul_overflow(n, (uint64_t)d, &n)) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s: element count overflows", t.name.c_str());
+        }
         const int be = type_block_elems(t.type), bb = type_block_bytes(t.type);
         if (bb == 0) { t.bytes = 0; t.data = nullptr; index_[t.name] = i; continue; }   // unknown type: only an error if used
         if (t.ne.empty() || t.ne[0] % be) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s: row length not a multiple of the block size", t.name.c_str());
-        t.bytes = (size_t)(n / be) * bb;
-        if (data_start + t.offset + t.bytes > size_) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s runs past the end of the file", t.name.c_str());
+        uint64_t bytes = 0;
+        if (__builtin_mul_overflow(n / (uint64_t)be, (uint64_t)bb, &bytes)) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s: byte size overflows", t.name.c_str());
+        if (t.offset % align) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s: offset %llu is not aligned to %llu", t.name.c_str(), (unsigned long long)t.offset, (unsigned long long)align);
+        if (t.offset > data_size || bytes > data_size - t.offset) B2_FAIL(B2_ERR_FORMAT, "gguf: tensor %s runs past the end of the file", t.name.c_str());
+        t.bytes = (size_t)bytes;
         t.data = map_ + data_start + t.offset;
         index_[t.name] = i;
     }
