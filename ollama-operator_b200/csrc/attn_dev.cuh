@@ -102,6 +102,10 @@ __device__ __forceinline__ float reduce8_lanes32(const float (&v)[8], int lane) 
 }
 __device__ __forceinline__ int reduce8_index(int lane) { return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1); }
 
+// The wide-row layout of the P.V product applies when the CTA's slice of the head is 32 or 64 dims and the per-chain
+// partial sums ([GRP][32][dpc] floats) stay small.
+template <int GRP> __host__ __device__ __forceinline__ bool pv_wide(int dpc) { return (dpc == 32 || dpc == 64) && GRP * dpc <= 128; }
+
 // Attention of one KV head (all GRP query heads that share it) by the NT calling threads of every
 // CTA of the cluster.  `xb` is this CTA's exchange barrier (initialised to `cluster` arrivals,
 // same shared-memory offset in every CTA), `xphase` its running phase; `barid` a CTA-local named
@@ -265,8 +269,72 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     }
     stamp(4);
 
-    // ---- 3. output dims of this CTA: V columns dotted with the probabilities, lane L = position mod 32 --
+    // ---- 3. output dims of this CTA: V columns dotted with the probabilities ------------------------------
+    // ggml's chain structure: for one output dim, positions t = c, c + 32, ... form FMA chain c (32 chains),
+    // combined by the fixed tree of reduce_lanes32.
     const int dpc = HD / CL, dbase = (int)rk * dpc;      // HD % (8 * CL) == 0 (checked on the host)
+    if (pv_wide<GRP>(dpc)) {
+        // Wide rows: `lpd` lanes cover the CTA's dims of one cached row (16 bytes each), so a warp load touches
+        // 32 / lpd whole row slices instead of 32 different rows (the L1 tag stage handles one 128-byte line per
+        // cycle: 16-byte pieces of 32 rows cost 32 cycles per load, and every row was visited by dpc / 8 warps).
+        // Warp w owns chains c = w * rpw + lane / lpd; a chain stays in one thread, in position order, so the sums
+        // are the ones the narrow layout below produces.  The 32 chain sums per dim meet in shared memory.
+        float* pvs = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(rowoff + maxc) + 15) & ~(uintptr_t)15);        // [GRP][32 chains][dpc]
+        const int lpd = dpc >> 3, rpw = 32 / lpd;
+        if (warp < lpd) {
+            const int dl = lane % lpd, c = warp * rpw + lane / lpd;
+            float acc[GRP][8];
+#pragma unroll
+            for (int g = 0; g < GRP; g++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc[g][j] = 0.f;
+            constexpr int UV = GRP >= 4 ? 4 : 8;        // V rows in flight per lane
+            for (int tb = c; tb < n; tb += 32 * UV) {
+                uint4 vv[UV];
+#pragma unroll
+                for (int u = 0; u < UV; u++) {
+                    const int t = min(tb + 32 * u, n - 1);
+                    vv[u] = *reinterpret_cast<const uint4*>(v_base + rowoff[t] + dbase + dl * 8);
+                }
+#pragma unroll
+                for (int u = 0; u < UV; u++) {
+                    const int t = tb + 32 * u;
+                    if (t < n) {
+                        const __half2* h2 = reinterpret_cast<const __half2*>(&vv[u]);
+                        float vf[8];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) { const float2 f = __half22float2(h2[j]); vf[2 * j] = f.x; vf[2 * j + 1] = f.y; }
+#pragma unroll
+                        for (int g = 0; g < GRP; g++) {
+                            const float p = sc[(size_t)g * maxc + t];
+#pragma unroll
+                            for (int j = 0; j < 8; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < GRP; g++) {
+                float4* dst = reinterpret_cast<float4*>(pvs + ((size_t)g * 32 + c) * dpc + dl * 8);
+                dst[0] = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
+                dst[1] = make_float4(acc[g][4], acc[g][5], acc[g][6], acc[g][7]);
+            }
+        }
+        named_bar_sync(barid, NT);
+        for (int o = tid; o < GRP * dpc; o += NT) {
+            const int g = o / dpc, d = o - g * dpc;
+            const float* v = pvs + (size_t)g * 32 * dpc + d;
+            float s4[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {       // lane c of reduce_lanes32 after the xor-16, 8, 4 steps
+                const float a0 = v[c * dpc] + v[(c + 16) * dpc], a1 = v[(c + 8) * dpc] + v[(c + 24) * dpc];
+                const float a2 = v[(c + 4) * dpc] + v[(c + 20) * dpc], a3 = v[(c + 12) * dpc] + v[(c + 28) * dpc];
+                s4[c] = (a0 + a1) + (a2 + a3);
+            }
+            a.out[((size_t)kvh * GRP + g) * HD + dbase + d] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        }
+    } else
+    {
     for (int d0 = 8 * warp; d0 < dpc; d0 += 8 * NWARP) {
         float acc[GRP][8];
 #pragma unroll
@@ -304,15 +372,18 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
             if ((lane & 3) == 0) a.out[((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane)] = r;
         }
     }
+    }
     stamp(5);
     named_bar_sync(barid, NT);      // the score buffer is free again (a following head reuses it)
 }
 
 static inline size_t attn_smem_bytes(int grp, int hd, int max_ctx_pad, int cluster, int nthreads) {
-    (void)cluster;
     const int nwarps = nthreads / 32;
+    const int dpc = cluster > 0 ? hd / cluster : hd;
+    // chain sums of the wide P.V layout (+ alignment slack); a GQA group may also be processed one query head at a time (GRP = 1)
+    const size_t pv = (dpc == 32 || dpc == 64) ? (size_t)(grp * dpc <= 128 ? grp : 1) * 32 * dpc + 4 : 0;
     const size_t d = (size_t)((nwarps * grp + 1) & ~1);                                        // doubles
-    const size_t f = (size_t)grp * hd + (size_t)grp * max_ctx_pad + (size_t)nwarps * grp + (size_t)max_ctx_pad;   // floats + row offsets
+    const size_t f = (size_t)grp * hd + (size_t)grp * max_ctx_pad + (size_t)nwarps * grp + (size_t)max_ctx_pad + pv;   // floats + row offsets
     return (d * sizeof(double) + f * sizeof(float) + 15) / 16 * 16;
 }
 

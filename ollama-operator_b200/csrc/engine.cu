@@ -893,11 +893,11 @@ int Model::mega_trace(int seq, int32_t tok, unsigned long long* out, int cap, in
     if (!s.mega_ok) B2_FAIL(B2_ERR_STATE, "mega_trace: the persistent kernel is not in use for this model");
     const int nst = s.mega.s_end - s.mega.s_begin, ncta = s.mega.grid;
     *n_cta = ncta; *n_stage = nst;
-    if (!out || cap < ncta * nst * 12) B2_FAIL(B2_ERR_ARG, "mega_trace: need room for %d values", ncta * nst * 12);
+    if (!out || cap < ncta * nst * 16) B2_FAIL(B2_ERR_ARG, "mega_trace: need room for %d values", ncta * nst * 16);
     B2_TRY(ensure_pages(s, s.len + 1));
     unsigned long long* d_tr = nullptr;
-    B2_CUDA(cudaMalloc(&d_tr, (size_t)ncta * nst * 12 * 8));
-    B2_CUDA(cudaMemset(d_tr, 0, (size_t)ncta * nst * 12 * 8));
+    B2_CUDA(cudaMalloc(&d_tr, (size_t)ncta * nst * 16 * 8));
+    B2_CUDA(cudaMemset(d_tr, 0, (size_t)ncta * nst * 16 * 8));
     SeqState st{};
     st.pos = s.len; st.cur_tok = tok;
     B2_CUDA(cudaMemcpyAsync(s.d_state, &st, sizeof(st), cudaMemcpyHostToDevice, stream));
@@ -906,7 +906,7 @@ int Model::mega_trace(int seq, int32_t tok, unsigned long long* out, int cap, in
     const int rc = enqueue_step(s, true, &nl, nullptr);
     s.mega.trace = nullptr;
     cudaStreamSynchronize(stream);
-    if (rc == B2_OK) cudaMemcpy(out, d_tr, (size_t)ncta * nst * 12 * 8, cudaMemcpyDeviceToHost);
+    if (rc == B2_OK) cudaMemcpy(out, d_tr, (size_t)ncta * nst * 16 * 8, cudaMemcpyDeviceToHost);
     cudaFree(d_tr);
     B2_TRY(rc);
     B2_CUDA(cudaMemcpy(&s.host, s.d_state, sizeof(SeqState), cudaMemcpyDeviceToHost));

@@ -95,6 +95,12 @@ __device__ __forceinline__ float div127_rn(float a) {
     return __fmaf_rn(r, c, q);
 }
 
+// (int)roundf(t) for |t| <= 256 (round half away from zero) in three instructions: add the largest float below
+// one half with the sign of t, then truncate.  Checked against roundf() for every float in that range on the host.
+__device__ __forceinline__ int round_away_i(float t) {
+    return __float2int_rz(__fadd_rn(t, copysignf(0x1.fffffep-2f, t)));
+}
+
 __device__ __forceinline__ uint32_t pack4(int a, int b, int c, int d) {
     return (uint32_t)(a & 0xFF) | ((uint32_t)(b & 0xFF) << 8) | ((uint32_t)(c & 0xFF) << 16) | ((uint32_t)(d & 0xFF) << 24);
 }
@@ -118,8 +124,8 @@ static __device__ __forceinline__ void prologue_q8_0_each(const GemvArgs& a, con
         amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
         const float d = div127_rn(amax);
         const float id = d != 0.0f ? __frcp_rn(d) : 0.0f;
-        const int q0 = (int)roundf(__fmul_rn(v.x, id)), q1 = (int)roundf(__fmul_rn(v.y, id));
-        const int q2 = (int)roundf(__fmul_rn(v.z, id)), q3 = (int)roundf(__fmul_rn(v.w, id));
+        const int q0 = round_away_i(__fmul_rn(v.x, id)), q1 = round_away_i(__fmul_rn(v.y, id));
+        const int q2 = round_away_i(__fmul_rn(v.z, id)), q3 = round_away_i(__fmul_rn(v.w, id));
         int sum = q0 + q1 + q2 + q3;
         sum += __shfl_xor_sync(gmask, sum, 1);
         sum += __shfl_xor_sync(gmask, sum, 2);

@@ -94,13 +94,14 @@ int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cud
 
 // ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
 constexpr int MEGA_NCW = 15;      // consumer warps per CTA
-struct MegaStage {                // one stage of the layer pipeline, resident in device memory
+struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident in device memory (copied to shared memory by 16-byte bulk copies)
     int kind = 0;                 // 0 = GEMV, 1 = attention, 2 = tensor-parallel exchange (all-reduce + residual)
     GemvArgs g;
     int S = 1;                    // warps along K per row
     int P = 2;                    // warps sharing a row pair (each takes every P-th row)
     int G = 1;                    // row groups per CTA (G * S * P <= MEGA_NCW)
-    int RPG = 2, RT = 2;          // rows per group per tile, rows per tile
+    int RPG = 2, RT = 2;          // rows per group per tile, rows per tile (= 2 * PT)
+    int PT = 1;                   // row pairs per tile (one ring slot); PT * S owner warps release a slot
     int nunits = 0, nbeff = 4;    // units per row, units per lane actually used
     AttnArgs at;
     int att_max_local = 0;

@@ -29,7 +29,10 @@ namespace {
 using namespace gemvdev;
 using namespace attndev;
 
-constexpr int MEGA_NS_MAX = 8;
+constexpr int MEGA_NS_MAX = 16;
+// Arrival units of a ring slot's `empty` barrier: every pair-slot owner warp of a tile arrives with
+// MEGA_EMPTY_BASE / (PT * S) units, so any tile shape with PT * S <= 15 owners completes the same barrier.
+constexpr uint32_t MEGA_EMPTY_BASE = 360360;      // lcm(1..15)
 constexpr int MEGA_MAX_PAGES = 256;
 
 struct MegaSmem {            // dynamic shared-memory carve-up (byte offsets), computed on the host
@@ -59,6 +62,7 @@ __device__ __forceinline__ void grid_barrier(unsigned* count, unsigned& epoch, i
         epoch++;
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(count) : "memory");
         const unsigned target = epoch * gridDim.x;
+        // (polling with relaxed loads plus one acquire fence was measured slower: 1.5-2.1 us per barrier against 1.2-1.5)
         while (ld_acquire_gpu(count) < target) {
         }
     }
@@ -120,13 +124,23 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     // position and page table of this step: fetched once, used by every layer's KV append and attention
     __shared__ int s_pos;
     __shared__ int s_pt[MEGA_MAX_PAGES];
+    // The stage table lives in global memory; a field read there costs an L2 round trip, and a stage reads a dozen
+    // of them in dependent steps (barrier -> operands -> strides -> loop bounds).  Each stage's descriptor is
+    // therefore copied into shared memory one stage ahead (bulk async copy, completion on dbar).
+    __shared__ __align__(16) uint8_t s_desc[2][sizeof(MegaStage)];
+    __shared__ uint64_t dbar[2];
     for (int i = tid; i < n_pages; i += blockDim.x) s_pt[i] = page_table[i];
     if (tid == 0) s_pos = *pos_ptr;
 
     if (tid == 0) {
-        for (int s = 0; s < sm.ns; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCW); }
+        for (int s = 0; s < sm.ns; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], MEGA_EMPTY_BASE); }
         mbar_init(xbar, cluster_size);
+        mbar_init(&dbar[0], 1); mbar_init(&dbar[1], 1);
         mbar_fence_init();
+        for (int i = 0; i < 2 && s_begin + i < s_end; i++) {
+            mbar_expect_tx(&dbar[i], (uint32_t)sizeof(MegaStage));
+            bulk_g2s_plain(s_desc[i], &stages[s_begin + i], (uint32_t)sizeof(MegaStage), &dbar[i]);
+        }
     }
     __syncthreads();
     cluster_sync_all();        // every CTA's exchange barrier exists before a peer can arrive on it
@@ -139,59 +153,68 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             // shared-memory ring, `p` runs up to sm.pf_bytes further ahead issuing L2 prefetches, so
             // that HBM keeps streaming while the consumers sit in a barrier, a prologue or the
             // attention (the ring alone covers ~3 us of HBM time, L2 holds tens of MB more)
+            // Everything a tile needs sits in registers once a cursor has entered a stage: the stage table is in
+            // global memory, and with tiles of a few KB a descriptor read per tile would bound the producer.
             struct Cursor {
-                int st; int64_t row0, r_end; int RT;
+                int st; int rows_left, RT;            // rows of this CTA still to issue in stage `st`
+                const uint8_t* pl[NP]; uint32_t stride[NP];
             };
             auto seek = [&](Cursor& c) {         // position on the first tile of the next GEMV stage at or after c.st
                 for (; c.st < s_end; c.st++) {
                     const MegaStage& S = stages[c.st];
                     if (S.kind != 0) continue;
-                    const int64_t pairs = S.g.W.rows >> 1;
-                    c.row0 = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x);
-                    c.r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
+                    const uint32_t pairs = (uint32_t)(S.g.W.rows >> 1);
+                    const uint32_t row0 = 2 * (blockIdx.x * pairs / gridDim.x), r_end = 2 * ((blockIdx.x + 1) * pairs / gridDim.x);
+                    if (row0 >= r_end) continue;
+                    c.rows_left = (int)(r_end - row0);
                     c.RT = S.RT;
-                    if (c.row0 < c.r_end) return;
+#pragma unroll
+                    for (int pl = 0; pl < NP; pl++) {
+                        const bool on = TYPE != T_KQ || pl < S.g.W.n_planes;
+                        c.stride[pl] = on ? S.g.W.stride[pl] : 0u;
+                        c.pl[pl] = on ? S.g.W.plane[pl] + (size_t)row0 * S.g.W.stride[pl] : nullptr;
+                    }
+                    return;
                 }
             };
             auto advance = [&](Cursor& c) {
-                c.row0 += c.RT;
-                if (c.row0 >= c.r_end) { c.st++; seek(c); }
+                c.rows_left -= c.RT;
+                if (c.rows_left <= 0) { c.st++; seek(c); return; }
+#pragma unroll
+                for (int pl = 0; pl < NP; pl++) c.pl[pl] += (size_t)c.RT * c.stride[pl];
             };
-            Cursor f{s_begin, 0, 0, 0}, p{s_begin, 0, 0, 0};
+            Cursor f, p;
+            f.st = p.st = s_begin; f.rows_left = p.rows_left = 0; f.RT = p.RT = 0;
             seek(f); seek(p);
             long long ahead = 0;                  // bytes prefetched to L2 but not yet requested for the ring
-            uint32_t it = 0;
+            uint32_t s = 0, lap = 0;              // ring slot of the next tile, times the ring has wrapped
             while (f.st < s_end) {
                 while (p.st < s_end && ahead < (long long)sm.pf_bytes) {
-                    const QMat& W = stages[p.st].g.W;
-                    const int rows_here = (int)min((int64_t)p.RT, p.r_end - p.row0);
+                    const uint32_t rows_here = (uint32_t)min(p.RT, p.rows_left);
 #pragma unroll
                     for (int pl = 0; pl < NP; pl++) {
-                        if (TYPE == T_KQ && pl >= W.n_planes) break;
-                        prefetch_l2(W.plane[pl] + (size_t)p.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl]);
-                        ahead += (long long)rows_here * W.stride[pl];
+                        if (p.stride[pl] == 0) continue;
+                        prefetch_l2(p.pl[pl], rows_here * p.stride[pl]);
+                        ahead += (long long)(rows_here * p.stride[pl]);
                     }
                     advance(p);
                 }
-                const QMat& W = stages[f.st].g.W;
-                const uint32_t s = it % sm.ns;
-                if (it >= (uint32_t)sm.ns) mbar_wait(&empty[s], ((it / sm.ns) - 1) & 1);
-                const int rows_here = (int)min((int64_t)f.RT, f.r_end - f.row0);
+                if (lap) mbar_wait(&empty[s], (lap - 1) & 1);
+                const uint32_t rows_here = (uint32_t)min(f.RT, f.rows_left);
                 uint32_t total = 0;
 #pragma unroll
-                for (int pl = 0; pl < NP; pl++)
-                    if (TYPE != T_KQ || pl < W.n_planes) total += (uint32_t)rows_here * W.stride[pl];
+                for (int pl = 0; pl < NP; pl++) total += rows_here * f.stride[pl];
                 mbar_expect_tx(&full[s], total);
                 uint8_t* dst = ring + (size_t)s * sm.stage_bytes;
 #pragma unroll
                 for (int pl = 0; pl < NP; pl++) {
-                    if (TYPE == T_KQ && pl >= W.n_planes) break;
-                    bulk_g2s(dst, W.plane[pl] + (size_t)f.row0 * W.stride[pl], (uint32_t)rows_here * W.stride[pl], &full[s], pol);
-                    dst += (size_t)f.RT * W.stride[pl];
+                    if (f.stride[pl] == 0) continue;
+                    bulk_g2s(dst, f.pl[pl], rows_here * f.stride[pl], &full[s], pol);
+                    dst += (size_t)f.RT * f.stride[pl];
                 }
                 ahead -= total;
                 advance(f);
-                it++;
+                if (++s == (uint32_t)sm.ns) { s = 0; lap++; }
             }
         }
         return;
@@ -199,21 +222,31 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
 
     // ===== consumers =====
     const int pos_now = s_pos;        // written before the __syncthreads above
-    uint32_t it = 0, xphase = 0;
+    uint32_t ring_slot = 0, ring_phase = 0, xphase = 0;      // ring position of the next stage's first tile
     unsigned epoch = 0;
     unsigned tp_epoch = TP ? *reinterpret_cast<volatile unsigned*>(tp.epoch) : 0u;      // exchanges completed before this launch
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
     constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
     for (int st = s_begin; st < s_end; st++) {
-        const MegaStage& S = stages[st];
+        const int db = (st - s_begin) & 1;
+        mbar_wait(&dbar[db], (uint32_t)((st - s_begin) >> 1) & 1u);
+        const MegaStage& S = *reinterpret_cast<const MegaStage*>(s_desc[db]);
+        // after this stage's grid barrier nobody reads the previous stage's descriptor any more: fetch the next one over it
+        auto fetch_next_desc = [&]() {
+            if (tid == 0 && st > s_begin && st + 1 < s_end) {
+                mbar_expect_tx(&dbar[db ^ 1], (uint32_t)sizeof(MegaStage));
+                bulk_g2s_plain(s_desc[db ^ 1], &stages[st + 1], (uint32_t)sizeof(MegaStage), &dbar[db ^ 1]);
+            }
+        };
         // optional per-stage timestamps (ns): [0] stage entered, [1] barrier passed, [2] prologue done, [3] stage done
-        unsigned long long* tr = trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 12 : nullptr;
+        unsigned long long* tr = trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 16 : nullptr;
         if (tr) tr[0] = global_ns();
 
         if (TP && S.kind == 2) {
             // ---- tensor-parallel exchange: x += (float)(sum over the GPUs of the K-split partial sums) ----
             // (tp.cu describes the protocol; here the publishing side is "all CTAs passed the grid barrier")
             grid_barrier(grid_count, epoch, tid, ntc);              // this GPU's partial sums are complete
+            fetch_next_desc();
             if (tr) tr[1] = global_ns();
             tp_epoch++;
             tp_exchange(tp, tp_epoch, S.tp_buf, S.tp_x, S.tp_n, tid, ntc);
@@ -222,6 +255,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         }
         if (S.kind != 0) {
             if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);
+            fetch_next_desc();
             if (tr) tr[1] = global_ns();
             // ---- attention: clusters take KV heads round-robin ----
             const AttnArgs& a = S.at;
@@ -256,6 +290,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             }
         }
         if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
+        fetch_next_desc();
         if (tr) { tr[1] = global_ns(); tr[10] = (unsigned long long)clock64(); }
 
         if (fast) {
@@ -301,8 +336,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
                     const float d = div127_rn(amax);
                     const float id = d != 0.0f ? __frcp_rn(d) : 0.0f;
-                    const int q0 = (int)roundf(__fmul_rn(v.x, id)), q1 = (int)roundf(__fmul_rn(v.y, id));
-                    const int q2 = (int)roundf(__fmul_rn(v.z, id)), q3 = (int)roundf(__fmul_rn(v.w, id));
+                    const int q0 = round_away_i(__fmul_rn(v.x, id)), q1 = round_away_i(__fmul_rn(v.y, id));
+                    const int q2 = round_away_i(__fmul_rn(v.z, id)), q3 = round_away_i(__fmul_rn(v.w, id));
                     int sum = q0 + q1 + q2 + q3;
                     sum += __shfl_xor_sync(gmask, sum, 1);
                     sum += __shfl_xor_sync(gmask, sum, 2);
@@ -339,42 +374,60 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         if (tr) { tr[2] = global_ns(); tr[9] = (unsigned long long)clock64(); }
         // the attention stage that follows will read K/V rows that already exist: pull them into L2
         // now, while this stage streams its weights
-        if (st + 1 < s_end && stages[st + 1].kind != 0) {
-            const AttnArgs& na = stages[st + 1].at;
+        bool next_is_attn = false;
+        if (st + 1 < s_end) {
+            mbar_wait(&dbar[db ^ 1], (uint32_t)((st + 1 - s_begin) >> 1) & 1u);      // issued a stage ago (or at kernel start)
+            next_is_attn = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->kind == 1;
+        }
+        if (next_is_attn) {
+            const AttnArgs& na = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->at;
             const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
             for (int kvh = my_cluster; kvh < na.n_head_kv; kvh += n_clusters) attn_prefetch<GRP, HD, ntc>(na, cluster_size, kvh, tid, pos_now, s_pt);
         }
 
-        const int64_t pairs = a.W.rows >> 1;
-        const int64_t r_begin = 2 * ((int64_t)blockIdx.x * pairs / gridDim.x), r_end = 2 * ((int64_t)(blockIdx.x + 1) * pairs / gridDim.x);
+        // rows [r_begin, r_end) of this CTA: whole pairs, split evenly (32-bit: pairs * grid < 2^31 for every supported matrix)
+        const uint32_t pairs = (uint32_t)(a.W.rows >> 1);
+        const int r_begin = (int)(2 * (blockIdx.x * pairs / gridDim.x)), r_end = (int)(2 * ((blockIdx.x + 1) * pairs / gridDim.x));
         // the stage descriptor lives in global memory and the waits below are compiler barriers: keep what
         // the row loop needs in registers
         uint32_t wstride[NP];
 #pragma unroll
         for (int p = 0; p < NP; p++) wstride[p] = TYPE != T_KQ || p < a.W.n_planes ? (uint32_t)a.W.stride[p] : 0u;
-        for (int64_t row0 = r_begin; row0 < r_end; row0 += RT, it++) {
-            const uint32_t s = it % sm.ns;
-            if (!(sm.debug & 2)) mbar_wait(&full[s], (it / sm.ns) & 1);
-            const int rows_here = (int)min((int64_t)RT, r_end - row0);
-            const uint8_t* sp = ring + (size_t)s * sm.stage_bytes;
-            if (working && !(sm.debug & 1)) {
-                // two rows at a time: twice the independent dp4a chains, and one transposed f64 butterfly
-                // (lanes 0-15 end up with row r, lanes 16-31 with row r+1) instead of two
-                for (int r = 2 * worker; r < rows_here; r += 2 * NW) {
+        // Row pairs of this CTA are handed out as "pair slots" j = 0, 1, ...: slot j belongs to tile j / PT (one ring
+        // slot, PT pairs, a few KB) and to row worker j % NW.  Small tiles keep the ring densely packed and let the
+        // producer refill as soon as PT owners are done instead of waiting for all fifteen warps.
+        const int PT = S.PT;
+        const int npairs_cta = (r_end - r_begin) >> 1;
+        const int ntiles = (npairs_cta + PT - 1) / PT;
+        const uint32_t arrive_units = MEGA_EMPTY_BASE / (uint32_t)(PT * Sw);
+        long long c_wait = 0, c_work = 0;      // (trace only) cycles warp 0 spends waiting for tiles / computing
+        if (working) {
+            // (tile, pair inside the tile, ring slot, slot phase) of this worker's pair slots, advanced without divisions
+            const int dq = NW / PT, dr = NW - dq * PT;
+            int t = worker / PT, i = worker - t * PT;
+            uint32_t slot = ring_slot + (uint32_t)t, phase = ring_phase;
+            while (slot >= (uint32_t)sm.ns) { slot -= sm.ns; phase ^= 1u; }
+            for (int j = worker; j < ntiles * PT; j += NW) {
+                const long long c0 = tr ? clock64() : 0;
+                if (!(sm.debug & 2)) mbar_wait(&full[slot], phase);
+                const long long c1 = tr ? clock64() : 0;
+                if (j < npairs_cta && !(sm.debug & 1)) {
+                    // two rows at a time: twice the independent dp4a chains, and one transposed f64 butterfly
+                    // (lanes 0-15 end up with row r, lanes 16-31 with row r+1) instead of two
+                    const uint8_t* pb = ring + slot * sm.stage_bytes;
+                    const uint32_t r = 2u * (uint32_t)i;
                     RowPtrs rp0, rp1;
-                    const uint8_t* pb = sp;
 #pragma unroll
                     for (int p = 0; p < NP; p++) {
-                        rp0.p[p] = pb + (uint32_t)r * wstride[p];
+                        rp0.p[p] = pb + r * wstride[p];
                         rp1.p[p] = rp0.p[p] + wstride[p];
                         pb += (uint32_t)RT * wstride[p];
                     }
-
                     double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
-                    for (int j = 0; j < NB; j++) {
-                        acc0 += (double)unit_dot(xr[j], rp0, unit[j], nunits);
-                        acc1 += (double)unit_dot(xr[j], rp1, unit[j], nunits);
+                    for (int jj = 0; jj < NB; jj++) {
+                        acc0 += (double)unit_dot(xr[jj], rp0, unit[jj], nunits);
+                        acc1 += (double)unit_dot(xr[jj], rp1, unit[jj], nunits);
                     }
                     const bool upper = (lane & 16) != 0;
                     double keep = upper ? acc1 : acc0;
@@ -382,12 +435,20 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     keep += __shfl_xor_sync(0xffffffffu, give, 16);
 #pragma unroll
                     for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
-                    if ((lane & 15) == 0) ysum[(size_t)(row0 - r_begin + r + (upper ? 1 : 0)) * Sw + ch] = keep;
+                    if ((lane & 15) == 0) ysum[(2 * j + (upper ? 1 : 0)) * Sw + ch] = keep;
                 }
+                __syncwarp();
+                if (lane == 0 && !(sm.debug & 2)) mbar_arrive_units(&empty[slot], arrive_units);       // this warp no longer reads the slot
+                if (tr) { const long long c2 = clock64(); c_wait += c1 - c0; c_work += c2 - c1; }
+                i += dr; slot += (uint32_t)dq;
+                if (i >= PT) { i -= PT; slot++; }
+                while (slot >= (uint32_t)sm.ns) { slot -= sm.ns; phase ^= 1u; }
             }
-            __syncwarp();
-            if (lane == 0 && !(sm.debug & 2)) mbar_arrive(&empty[s]);       // this warp no longer reads stage s
         }
+        if (tr) { tr[12] = (unsigned long long)c_wait; tr[13] = (unsigned long long)c_work; }
+        ring_slot += (uint32_t)ntiles;
+        while (ring_slot >= (uint32_t)sm.ns) { ring_slot -= sm.ns; ring_phase ^= 1u; }
+        if (tr) tr[11] = (unsigned long long)clock64();           // (this warp's row loop done)
         // ---- deferred epilogue: all row sums of this CTA are in shared memory; one thread per row pair,
         //      so the long-latency parts (f64 exp of SiLU, RoPE table, KV page lookup) are paid once ----
         named_bar_sync(1, ntc);
@@ -418,6 +479,10 @@ int g_mega_sms = 0;
 // ---- host side ---------------------------------------------------------------------------------------
 // Estimated consumer cost of a stage per row pair: (units per lane x 2 rows x ~27 instructions + the f64
 // butterfly, ~35) spread over the G row workers -- the model behind the choice of units per lane.
+static int mega_tile_target() {
+    static const int v = getenv("B2_MEGA_TILE_KB") ? atoi(getenv("B2_MEGA_TILE_KB")) * 1024 : 72 * 1024;
+    return v;
+}
 static double plan_cost(int nunits, int nbe, int ncw, int* S_out, int* G_out) {
     const int S = (nunits + 32 * nbe - 1) / (32 * nbe);
     if (S > ncw) return 1e30;
@@ -448,13 +513,14 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
         if (c < best) { best = c; best_idle = 0; st.nbeff = nbe; st.S = S; st.G = G; }
     }
     if (best_idle == (1 << 30)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: k=%lld does not map onto %d consumer warps", (long long)W.k, ncw);
-    // tile = a whole number of worker rounds, close to 36 KB
+    // tile = PT row pairs, up to 72 KB (one bulk copy per plane: a single producer thread issues about three
+    // tiles per microsecond, so small tiles would bound the stream); PT * S owner warps (<= 15) release a tile
     size_t rb = 0;
     for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
-    int rounds = (int)((40 * 1024) / (rb * st.G * 2));
-    if (rounds < 1) rounds = 1;
-    st.RT = rounds * st.G * 2;           // every worker takes two rows per round
-    while ((size_t)st.RT * rb > 72 * 1024 && st.RT > 2) st.RT -= 2;      // heavy rows (Q6_K): two stages must still fit the ring; some workers idle
+    int pt = (int)((size_t)mega_tile_target() / (2 * rb));
+    pt = std::max(1, std::min(pt, std::max(1, 15 / st.S)));
+    st.PT = pt;
+    st.RT = 2 * pt;
     st.P = 1; st.RPG = 0;
     return B2_OK;
 }
@@ -503,6 +569,14 @@ static int mega_occupancy_t(const MegaLaunch& L, int* max_clusters) {
     return B2_OK;
 }
 
+template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
+static int mega_static_smem_t(const MegaLaunch&, size_t* out) {
+    cudaFuncAttributes fa;
+    B2_CUDA(cudaFuncGetAttributes(&fa, mega_kernel<TYPE, NB, NCW, GRP, HD, TP>));
+    *out = fa.sharedSizeBytes;
+    return B2_OK;
+}
+
 #define B2_MEGA_CASE(FN, G, H, ...)                                                                        \
     if (L.type == T_Q4_0 && L.grp == G && L.head_dim == H && L.nb == 4)                                    \
         return L.tp.n > 1 ? FN<T_Q4_0, 4, MEGA_NCW, G, H, true>(__VA_ARGS__) : FN<T_Q4_0, 4, MEGA_NCW, G, H, false>(__VA_ARGS__); \
@@ -547,7 +621,12 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     off = (off + 127) / 128 * 128;
     L.off_ring = (uint32_t)off;
     L.stage_bytes = (uint32_t)((tile_bytes_max + 127) / 128 * 128);
-    const size_t cap = 225 * 1024;          // 227 KB per CTA minus the kernel's static shared memory (page table copy)
+    size_t static_smem = 0;                 // page table copy, stage descriptors
+    {
+        auto q = [&](size_t* o) -> int { B2_MEGA_DISPATCH(mega_static_smem_t, L, o); B2_FAIL(B2_ERR_UNSUPPORTED, "mega: dispatch"); };
+        B2_TRY(q(&static_smem));
+    }
+    const size_t cap = (227 * 1024 - static_smem) / 128 * 128;          // 227 KB per CTA minus the kernel's static shared memory
     if (off + 2 * (size_t)L.stage_bytes > cap) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: shared memory does not fit (%zu B before the ring, %u B per stage)", off, L.stage_bytes);
     L.ns = (int)std::min<size_t>(MEGA_NS_MAX, (cap - off) / L.stage_bytes);
     L.smem_bytes = off + (size_t)L.ns * L.stage_bytes;

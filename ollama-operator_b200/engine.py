@@ -277,13 +277,13 @@ class Model:
         return out
 
     def mega_trace(self, seq: int, tok: int) -> np.ndarray:
-        """Per-CTA, per-stage time stamps (ns) of one step of the persistent kernel: [cta][stage][12]
+        """Per-CTA, per-stage time stamps (ns) of one step of the persistent kernel: [cta][stage][16]
         (0-3 stage entered / barrier passed / prologue done / stage done; 4-11 attention phases)."""
-        cap = 160 * (self.info.n_layer * 6) * 12
+        cap = 160 * (self.info.n_layer * 6) * 16
         out = np.zeros(cap, dtype=np.uint64)
         nc, ns = C.c_int(0), C.c_int(0)
         _check(lib().b2_mega_trace(self._h, seq, tok, _ptr(out), cap, C.byref(nc), C.byref(ns)))
-        return out[: nc.value * ns.value * 12].reshape(nc.value, ns.value, 12)
+        return out[: nc.value * ns.value * 16].reshape(nc.value, ns.value, 16)
 
     def stats(self) -> Stats:
         s = Stats()

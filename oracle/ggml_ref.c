@@ -51,6 +51,16 @@ int ref_num_threads(void) {
 #endif
 }
 
+/* A launcher may export OMP_NUM_THREADS=1 for its workers (torch.distributed.run does); the timed CPU
+ * baseline sets the count it wants explicitly. */
+void ref_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ---- dequantisation ------------------------------------------------------------- */
 /* Q4_0: w[j] = (qs[j] & 15) - 8, w[j+16] = (qs[j] >> 4) - 8, times d  (gguf/quants.py:241-251) */
 static void dq_q4_0(const blk_q4_0 *x, float *y, int64_t k) {
@@ -508,6 +518,44 @@ static double canon_dot_q4_K(int64_t n, const blk_q4_K *x, const blk_q8_K *y) {
     return acc;
 }
 
+/* ---- mode 3: the SAME arithmetic in the order of ggml's AVX2 kernels [upstream ggml_vec_dot_q4_0_q8_0 /
+ * ggml_vec_dot_q8_0_q8_0, AVX2 branch]: per block d = d_w * d_a in f32, the 32 byte products folded into eight
+ * int32 lanes (maddubs + madd: lane l = bytes 4l..4l+3 of [low nibbles | high nibbles]), acc[l] = fma(d, lane, acc[l]),
+ * and hsum_float_8 at the end.  It exists to measure how far two legitimate ggml builds drift apart
+ * (the noise floor any other implementation is judged against); nothing is pinned to it. */
+static float avx2_hsum8(const float a[8]) {
+    const float r0 = a[0] + a[4], r1 = a[1] + a[5], r2 = a[2] + a[6], r3 = a[3] + a[7];
+    return (r0 + r2) + (r1 + r3);
+}
+static float avx2order_dot_q4_0(int64_t n, const blk_q4_0 *x, const blk_q8_0 *y) {
+    float acc[8] = {0};
+    for (int64_t i = 0; i < n / 32; i++) {
+        const float d = h2f(x[i].d) * h2f(y[i].d);
+        for (int l = 0; l < 8; l++) {
+            int s = 0;
+            for (int j = 0; j < 4; j++) {
+                const int b = 4 * l + j;                    /* byte of the 32-byte vector [lo nibbles | hi nibbles] */
+                const int w = b < 16 ? (x[i].qs[b] & 0x0F) - 8 : (x[i].qs[b - 16] >> 4) - 8;
+                s += w * y[i].qs[b];
+            }
+            acc[l] = fmaf(d, (float)s, acc[l]);
+        }
+    }
+    return avx2_hsum8(acc);
+}
+static float avx2order_dot_q8_0(int64_t n, const blk_q8_0 *x, const blk_q8_0 *y) {
+    float acc[8] = {0};
+    for (int64_t i = 0; i < n / 32; i++) {
+        const float d = h2f(x[i].d) * h2f(y[i].d);
+        for (int l = 0; l < 8; l++) {
+            int s = 0;
+            for (int j = 0; j < 4; j++) s += x[i].qs[4 * l + j] * y[i].qs[4 * l + j];
+            acc[l] = fmaf(d, (float)s, acc[l]);
+        }
+    }
+    return avx2_hsum8(acc);
+}
+
 /* vec_dot_type of each weight type (ggml type_traits [upstream]) */
 static int act_type_for(int wtype) {
     switch (wtype) {
@@ -559,6 +607,11 @@ void ref_mul_mat_vec(int wtype, const void *W, int64_t rows, int64_t k, const fl
             case REF_Q6_K: y[r] = (float)canon_dot_q6_K(k, (const blk_q6_K *)wr, (const blk_q8_K *)xq); break;
             default: y[r] = 0;
             }
+            continue;
+        }
+        if (faithful == 3 && (wtype == REF_Q4_0 || wtype == REF_Q8_0)) {
+            y[r] = wtype == REF_Q4_0 ? avx2order_dot_q4_0(k, (const blk_q4_0 *)wr, (const blk_q8_0 *)xq)
+                                     : avx2order_dot_q8_0(k, (const blk_q8_0 *)wr, (const blk_q8_0 *)xq);
             continue;
         }
         switch (wtype) {

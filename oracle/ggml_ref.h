@@ -67,6 +67,9 @@ float ref_vec_dot_q6_K_q8_K(int64_t n, const void *vx, const void *vy);
  *   2  "canonical": the same terms, added in f64 and rounded to f32 once, exp/tanh rounded
  *      from f64 -- order-free, so the CUDA kernels can (and must) match it bit for bit.  (The
  *      attention dots of mode 2 follow ggml's 32-lane SIMD f16 dot instead; see ggml_ref.c.)
+ *   3  mode 1 with the Q4_0 / Q8_0 dots in the order of ggml's AVX2 kernels (d_w*d_a first, eight
+ *      fma lanes, hsum_float_8): a second legitimate ggml build, used only to measure how far two
+ *      such builds drift apart end to end (bench.py `ggml_build_noise`).
  * threads<=0 -> all cores. */
 void ref_mul_mat_vec(int wtype, const void *W, int64_t rows, int64_t k,
                      const float *x, float *y, int faithful, int threads);
@@ -119,6 +122,7 @@ int ref_eval(ref_ctx *c, int32_t token, int pos, float *logits);
 const float *ref_last_hidden(const ref_ctx *c);
 
 int ref_num_threads(void);
+void ref_set_num_threads(int n);     /* overrides OMP_NUM_THREADS for later calls with threads == 0 */
 
 #ifdef __cplusplus
 }

@@ -79,6 +79,7 @@ def lib() -> C.CDLL:
         L.ref_last_hidden.restype = fp
         L.ref_last_hidden.argtypes = [vp]
         L.ref_num_threads.restype = C.c_int
+        L.ref_set_num_threads.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -145,7 +146,8 @@ class OracleModel:
     """A GGUF file opened with the `gguf` package's reader and evaluated by the C oracle."""
 
     def __init__(self, path: str, faithful: int = 1, threads: int = 0, n_ctx: int | None = None):
-        """faithful: 0 ideal f32, 1 ggml generic C order, 2 canonical (f64 term accumulation; see ggml_ref.h)."""
+        """faithful: 0 ideal f32, 1 ggml generic C order, 2 canonical (f64 term accumulation; see ggml_ref.h),
+        3 ggml AVX2 kernel order for Q4_0/Q8_0 matrices (a second legitimate ggml build: noise-floor measurements)."""
         import gguf
         self.reader = r = gguf.GGUFReader(path)
         self.tensors = {t.name: t for t in r.tensors}

@@ -37,3 +37,10 @@ for k, nm in ((0, "qkv"), (3, "up"), (4, "down")):
     pts = np.where(pts == 0, np.nan, pts)
     print(f"prologue {nm}: barrier->loads issued, ->x arrived+squares, ->stats, ->quantised, ->bar, ->xregs (us):", np.round(np.nanmean(np.diff(pts, axis=1), 0) / 1.9e3, 2), '(SM cycles / 1.9 GHz)')
 
+
+for k, nm in ((0, "qkv"), (2, "wo"), (3, "up"), (4, "down")):
+    g = tr[:, 15 * 5 + k, :]
+    loop = (g[:, 11] - g[:, 9]) / 1.9e3
+    tail = (g[:, 3] - g[:, 2]) / 1e3 - loop
+    print(f"body {nm}: warp 0 waits for tiles {(g[:, 12] / 1.9e3).mean():.2f} us, computes {(g[:, 13] / 1.9e3).mean():.2f} us")
+    print(f"body {nm}: warp 0 row loop mean {loop.mean():.2f} max {loop.max():.2f} us; rest of the body (wait for the other warps + epilogue) mean {tail.mean():.2f} max {tail.max():.2f} us")

@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(512, 1) k(const uint8_t* gq, const uint8_t* gs
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp >= nact) return;
+    asm volatile("bar.sync 1, %0;" :: "r"(nact * 32));
     X x[4]; int unit[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -134,7 +135,7 @@ template <int V> void run(const char* name, const uint8_t* gq, const uint8_t* gs
     const int smem = RT * (QS + SS);
     CK(cudaFuncSetAttribute(k<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     static long long h[148 * 16];
-    for (int nact : {1, 4, 8, 12, 15, 16}) {
+    for (int nact : {1, 8, 15}) {
         k<V><<<148, 512, smem>>>(gq, gs, iters, nact, dout, sink);
         CK(cudaDeviceSynchronize());
         CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
@@ -152,6 +153,7 @@ int main() {
     uint8_t *gq, *gs; long long* dout; double* sink;
     CK(cudaMalloc(&gq, nq)); CK(cudaMalloc(&gs, ns)); CK(cudaMalloc(&dout, 148 * 16 * 8)); CK(cudaMalloc(&sink, 8));
     CK(cudaMemcpy(gq, hq, nq, cudaMemcpyHostToDevice)); CK(cudaMemcpy(gs, hs, ns, cudaMemcpyHostToDevice));
+    for (int it : {1, 2, 4, 6, 12}) { printf("-- short runs: %d iterations per warp (cold start after a block barrier)\n", it); run<0>("V0 short", gq, gs, dout, sink, it); run<2>("V2 short", gq, gs, dout, sink, it); }
     const int iters = 400;
     run<0>("V0 current (f64, 2 rows)", gq, gs, dout, sink, iters);
     run<1>("V1 f32 accumulate", gq, gs, dout, sink, iters);
