@@ -228,11 +228,12 @@ int b2_debug_read(b2_model* m, int seq, int what, float* out, int n) {
     const HParams& h = m->m.hp;
     const float* src = nullptr;
     int cap = 0;
+    // shard 0's buffers: under tensor parallelism q / att / h hold this shard's heads and FFN rows only
     switch (what) {
     case 0: src = s.x; cap = h.n_embd; break;
-    case 1: src = s.q; cap = h.n_head * h.head_dim; break;
-    case 2: src = s.att; cap = h.n_head * h.head_dim; break;
-    case 3: src = s.h; cap = h.n_ff; break;
+    case 1: src = s.q; cap = m->m.n_head_l * h.head_dim; break;
+    case 2: src = s.att; cap = m->m.n_head_l * h.head_dim; break;
+    case 3: src = s.h; cap = m->m.n_ff_l; break;
     case 4: src = s.logits; cap = h.n_vocab; break;
     case 5: src = s.att2; cap = h.n_embd; break;
     default: B2_FAIL(B2_ERR_ARG, "b2_debug_read: unknown buffer %d", what);
@@ -244,6 +245,8 @@ int b2_debug_read(b2_model* m, int seq, int what, float* out, int n) {
 }
 int b2_mega_trace(b2_model* m, int seq, int32_t tok, uint64_t* out, int cap, int* n_cta, int* n_stage) {
     if (!n_cta || !n_stage) B2_FAIL(B2_ERR_ARG, "b2_mega_trace: null argument");
+    // a traced step runs shard 0 alone; its in-kernel exchange stages would wait for peers that never launch
+    if (m && m->m.tp_size > 1) B2_FAIL(B2_ERR_UNSUPPORTED, "b2_mega_trace: not available for tensor-parallel models");
     B2_MODEL_CALL(m, m->m.mega_trace(seq, tok, (unsigned long long*)out, cap, n_cta, n_stage));
 }
 int b2_get_stats(const b2_model* m, b2_stats* out) {

@@ -247,7 +247,7 @@ int launch_batch_staged(const AttnArgs* d_args, const AttnArgs& a, int B, cudaSt
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = batch_pdl_enabled() ? 1 : 0;
     B2_CUDA(cudaLaunchKernelEx(&cfg, kern, d_args, maxc));
     return B2_OK;
 }

@@ -21,6 +21,12 @@
 
 namespace b2 {
 
+bool& batch_pdl_enabled() {
+    static bool on = true;
+    return on;
+}
+
+
 namespace {
 using namespace gemvdev;
 
@@ -86,7 +92,7 @@ int quant_cols_launch(const float* x, int64_t x_stride, int64_t K, int B, int pr
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = batch_pdl_enabled() ? 1 : 0;
     B2_CUDA(cudaLaunchKernelEx(&cfg, quant_cols_kernel, a, x_stride, out));
     return B2_OK;
 }

@@ -192,6 +192,19 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
 
     max_batch = o && o->max_batch > 0 ? o->max_batch : 1;
     max_ctx = o && o->max_ctx > 0 ? std::min(o->max_ctx, hp.n_ctx) : hp.n_ctx;
+    {   // The decode attention keeps the scores of every cached position (per query head of a KV group) plus a row-offset
+        // table in shared memory: (grp + 1) * 4 bytes per position out of ~200 KB.  Refuse a context it cannot serve at
+        // load time (and before the KV cache is allocated) instead of failing every later call; a file that only
+        // advertises a long context (Llama-3.1: 131072) is clamped when the caller did not ask for a size.
+        const int grp_q = hp.n_head / hp.n_head_kv;
+        const int ctx_limit = (int)((196 * 1024) / ((size_t)(grp_q + 1) * 4)) / 64 * 64;
+        if (o && o->max_ctx > 0) {
+            if (max_ctx > ctx_limit)
+                B2_FAIL(B2_ERR_UNSUPPORTED, "max_ctx %d is beyond what the decode attention serves for %d query heads per KV head (%d tokens)", max_ctx, grp_q, ctx_limit);
+        } else {
+            max_ctx = std::min(max_ctx, std::min(ctx_limit, 8192));
+        }
+    }
     if (tp_size > 1) {
         if (hp.arch != 0) B2_FAIL(B2_ERR_UNSUPPORTED, "tensor parallelism is built for the llama graph only");
         if (hp.n_head % tp_size || hp.n_head_kv % tp_size || hp.n_ff % tp_size || (hp.n_ff / tp_size) % 32)
@@ -380,17 +393,34 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
         s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
         s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced); s.d_grid_count = (unsigned*)(b + o_gc);
     }
-    // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (theta starts
-    // at pos and is multiplied by freq_base^(-2/n_rot) once per pair; libm cosf/sinf)
+    // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (ggml_rope_cache_init with
+    // ext_factor 0: theta_base starts at pos and is multiplied by freq_base^(-2/n_rot) once per pair; the angle is
+    // freq_scale * (theta_base / freq_factor[pair]); libm cosf/sinf).  `rope_freqs.weight` (Llama-3.1/3.2) holds the
+    // per-pair factors, `<arch>.rope.scaling.type = linear` divides positions by the scaling factor; yarn is refused.
     {
-        const float theta_scale = powf(hp.rope_freq_base, -2.0f / hp.n_rot);
+        const std::string arch = hp.arch == 0 ? "llama" : "phi2";
+        std::string stype;
+        float freq_scale = 1.0f;
+        if (f.get_str(arch + ".rope.scaling.type", &stype) && stype != "none") {
+            if (stype != "linear") B2_FAIL(B2_ERR_UNSUPPORTED, "rope scaling type '%s' is not supported (none, linear)", stype.c_str());
+            double fac = 1.0;
+            if (f.get_f64(arch + ".rope.scaling.factor", &fac) && fac > 0.0) freq_scale = 1.0f / (float)fac;
+        }
         const int half = hp.n_rot / 2;
+        std::vector<float> factors;
+        if (const GgufTensor* t = f.find("rope_freqs.weight")) {
+            if (t->type != T_F32 || t->ne.size() != 1 || t->ne[0] != half) B2_FAIL(B2_ERR_FORMAT, "rope_freqs.weight must be f32[%d]", half);
+            factors.assign((const float*)t->data, (const float*)t->data + half);
+        }
+        const float theta_scale = powf(hp.rope_freq_base, -2.0f / hp.n_rot);
         std::vector<float2> tab((size_t)max_ctx * half);
         for (int pos = 0; pos < max_ctx; pos++) {
-            float theta = (float)pos;
+            float theta_base = (float)pos;
             for (int p = 0; p < half; p++) {
+                const float ff = factors.empty() ? 1.0f : factors[p];
+                const float theta = freq_scale * (theta_base / ff);
                 tab[(size_t)pos * half + p] = make_float2(cosf(theta), sinf(theta));
-                theta *= theta_scale;
+                theta_base *= theta_scale;
             }
         }
         B2_CUDA(cudaMalloc(&rope_table, tab.size() * sizeof(float2)));

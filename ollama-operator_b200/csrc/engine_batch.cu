@@ -105,6 +105,7 @@ int Model::setup_batch() {
 int Model::batch_step(int B, const int* col_slot, const int* col_pos, const int32_t* col_tok, uint32_t head_mask) {
     if (!bt.ok) B2_FAIL(B2_ERR_STATE, "batched kernels are not available for this model");
     if (B < 1 || B > BATCH_MAX) B2_FAIL(B2_ERR_ARG, "batch_step: %d columns", B);
+    batch_pdl_enabled() = use_pdl;              // B2_LOAD_NO_PDL covers the batched launches too
     if (bt.next_region >= bt.n_regions) {          // all upload regions of this call are in flight: drain
         B2_CUDA(cudaStreamSynchronize(stream));
         bt.next_region = 0;

@@ -291,7 +291,7 @@ int gemm_launch_t(const GemmMaps& maps, const Q8Cols& x, int rows, int nbk, int 
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = batch_pdl_enabled() ? 1 : 0;
     B2_CUDA(cudaLaunchKernelEx(&cfg, kern, maps, x, rows, nbk, B, colargs, pos, pt, pt_stride));
     return B2_OK;
 }

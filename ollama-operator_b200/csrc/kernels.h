@@ -163,6 +163,9 @@ int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl);
 
 // ---- batch.cu / gemm.cu: several columns (tokens) per weight pass: batched decode and chunked prefill ----
 namespace b2 {
+// Programmatic dependent launch for the batched-step kernels (quantise, GEMM, attention): on unless the model was
+// loaded with B2_LOAD_NO_PDL; the engine sets it before it enqueues a batched step.
+bool& batch_pdl_enabled();
 constexpr int BATCH_MAX = 32;          // columns per pass (four 8-column MMA tiles)
 constexpr int GEMM_KC = 16;            // 32-weight blocks per K chunk (one pipeline stage of the batched kernel)
 constexpr int GEMM_XCOL = 2 * GEMM_KC * 16 + 16;   // bytes of one column's K chunk, padded (conflict-free B-fragment loads)

@@ -35,7 +35,9 @@ constexpr size_t kScratchBytes = (size_t)B2_NOALLOC_SCRATCH_BYTES;
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
 
 constexpr int kMaxDevices = 64;
-unsigned char* g_scratch_ptr[kMaxDevices] = {};   // device address of the array, per device
+// Device address of the array, per device.  Written without a lock: two threads that race on a device's first call
+// both store the same address (cudaGetSymbolAddress is deterministic per device), so the race is benign.
+unsigned char* g_scratch_ptr[kMaxDevices] = {};
 
 // Set-up, once per device, with that device current.
 int scratch_base(unsigned char** out) {
@@ -67,6 +69,11 @@ extern "C" int b2_gemv_noalloc(int ggml_type, const void* W, int64_t rows, int64
     if (rows <= 0 || k <= 0 || k % type_block_elems(ggml_type) || (rows & 1))
         B2_FAIL(B2_ERR_ARG, "b2_gemv_noalloc: rows=%lld must be positive and even, k=%lld a positive multiple of %d", (long long)rows, (long long)k,
                 type_block_elems(ggml_type));
+    // a row count or length beyond the scratch itself can never fit; refusing it here also keeps the byte
+    // arithmetic below far from wrapping (each product is then below 2^23 * 2^25)
+    if ((uint64_t)rows > kScratchBytes || (uint64_t)k > kScratchBytes * 4)
+        B2_FAIL(B2_ERR_NOMEM, "b2_gemv_noalloc: a %lld x %lld matrix cannot fit the %zu-byte static scratch; use b2_gemv", (long long)rows, (long long)k,
+                kScratchBytes);
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) {
         cudaGetLastError();

@@ -42,6 +42,8 @@ class ModelConfig:
     n_rot: int | None = None     # default head_dim (llama) / given (phi2)
     norm_eps: float = 1e-5
     rope_freq_base: float = 10000.0
+    rope_scaling: float = 1.0    # > 1: `rope.scaling.type = linear` with this factor (positions divided by it)
+    rope_factors: bool = False   # write `rope_freqs.weight` (Llama-3.1-style per-pair frequency factors)
     ftype: str = "q4_0"          # "q4_0" | "q4_k_m" | "q8_0"
     head_type: str | None = None  # default: q6_k when n_embd % 256 == 0 else body type
     name: str = "synthetic"
@@ -57,6 +59,7 @@ PRESETS = {
     "tiny-gqa": ModelConfig(n_head=8, n_head_kv=2, n_embd=512, n_ff=1024, ftype="q4_k_m"),
     "tiny-phi2": ModelConfig(arch="phi2", n_embd=256, n_head=4, n_head_kv=4, n_ff=1024, n_rot=32),
     "tiny-phi2-80": ModelConfig(arch="phi2", n_embd=320, n_head=4, n_head_kv=4, n_ff=1280, n_rot=32),      # phi-2's head_dim 80
+    "tiny-rope31": ModelConfig(rope_freq_base=500000.0, rope_scaling=4.0, rope_factors=True),   # Llama-3.1-style rope_freqs + linear scaling
     "tiny-gqa8": ModelConfig(n_head=16, n_head_kv=2, n_embd=2048, n_ff=2048),      # 70B's head layout (8 query heads per KV head, head_dim 128), Q4_0
     "llama2-7b": ModelConfig(n_layer=32, n_embd=4096, n_head=32, n_head_kv=32, n_ff=11008, n_vocab=32000, n_ctx=4096, name="llama2-7b"),
     "mistral-7b": ModelConfig(n_layer=32, n_embd=4096, n_head=32, n_head_kv=8, n_ff=14336, n_vocab=32000, n_ctx=4096, ftype="q4_k_m", name="mistral-7b"),
@@ -156,6 +159,9 @@ def write_gguf(path: str, cfg: ModelConfig, seed: int = 0x5EED, source: str = "g
     w.add_head_count_kv(HK)
     w.add_rope_dimension_count(n_rot)
     w.add_rope_freq_base(cfg.rope_freq_base)
+    if cfg.rope_scaling != 1.0:
+        w.add_rope_scaling_type(gguf.RopeScalingType.LINEAR)
+        w.add_rope_scaling_factor(cfg.rope_scaling)
     if cfg.arch == "llama":
         w.add_layer_norm_rms_eps(cfg.norm_eps)
     else:
@@ -195,6 +201,8 @@ def write_gguf(path: str, cfg: ModelConfig, seed: int = 0x5EED, source: str = "g
             quant(p + "ffn_down", E, F, F ** -0.5)
             vec(p + "ffn_down.bias", E, 0.0, 0.02)
     vec("output_norm.weight", E, 1.0, 0.02)
+    if cfg.rope_factors:       # low frequencies stretched by up to 8x, high ones kept (the shape of the Llama-3.1 factors)
+        w.add_tensor("rope_freqs.weight", np.linspace(1.0, 8.0, n_rot // 2).astype(np.float32))
     if cfg.arch == "phi2":
         vec("output_norm.bias", E, 0.0, 0.02)
     # head scaled so logits have std of a few units: keeps greedy margins well above tolerance

@@ -652,14 +652,19 @@ void ref_layer_norm(const float *x, const float *g, const float *b, float *y, in
     for (int64_t i = 0; i < n; i++) y[i] = (y[i] * scale) * g[i] + (b ? b[i] : 0.0f);
 }
 /* ggml rope [upstream]: theta starts at pos and is multiplied by base^(-2/n_rot) per pair */
-void ref_rope(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode) {
+void ref_rope_ext(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode, float freq_scale, const float *factors) {
+    /* ggml_rope_cache_init / rope_yarn with ext_factor = 0, attn_factor = 1 [upstream]: theta_base starts at pos and
+     * is multiplied by base^(-2/n_rot) per pair; the angle used is freq_scale * (theta_base / freq_factor[pair]) */
     const float theta_scale = powf(freq_base, -2.0f / n_rot);
+    if (freq_scale == 0.0f) freq_scale = 1.0f;
     for (int h = 0; h < n_head; h++) {
         float *v = x + (size_t)h * head_dim;
-        float theta = (float)pos;
+        float theta_base = (float)pos;
         for (int i0 = 0; i0 < n_rot; i0 += 2) {
+            const float ff = factors ? factors[i0 / 2] : 1.0f;
+            const float theta = freq_scale * (theta_base / ff);
             const float c = cosf(theta), s = sinf(theta);
-            theta *= theta_scale;
+            theta_base *= theta_scale;
             if (mode == 0) {
                 const float a = v[i0], b = v[i0 + 1];
                 v[i0] = a * c - b * s;
@@ -672,6 +677,9 @@ void ref_rope(float *x, int n_head, int head_dim, int n_rot, int pos, float freq
             }
         }
     }
+}
+void ref_rope(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode) {
+    ref_rope_ext(x, n_head, head_dim, n_rot, pos, freq_base, mode, 1.0f, NULL);
 }
 /* ggml soft_max [upstream]: max, expf(x-max), f64 sum, scale by 1/sum */
 void ref_softmax(float *x, int64_t n) {
@@ -900,8 +908,8 @@ int ref_eval(ref_ctx *c, int32_t token, int pos, float *logits) {
             matvec(c, &L->wq, qdim, E, c->xn, c->q);
             matvec(c, &L->wk, nkv, E, c->xn, c->k);
             matvec(c, &L->wv, nkv, E, c->xn, c->v);
-            ref_rope(c->q, m->n_head, hd, m->n_rot, pos, m->rope_freq_base, 0);
-            ref_rope(c->k, m->n_head_kv, hd, m->n_rot, pos, m->rope_freq_base, 0);
+            ref_rope_ext(c->q, m->n_head, hd, m->n_rot, pos, m->rope_freq_base, 0, m->rope_freq_scale, m->rope_factors);
+            ref_rope_ext(c->k, m->n_head_kv, hd, m->n_rot, pos, m->rope_freq_base, 0, m->rope_freq_scale, m->rope_factors);
             store_kv(c, il, pos);
             attend(c, il, pos, 1.0f / sqrtf((float)hd));
             matvec(c, &L->wo, E, qdim, c->att, c->proj);
@@ -919,10 +927,10 @@ int ref_eval(ref_ctx *c, int32_t token, int pos, float *logits) {
             add_bias(c->q, &L->bq, qdim + 2 * nkv);
             memcpy(c->k, c->q + qdim, nkv * 4);
             memcpy(c->v, c->q + qdim + nkv, nkv * 4);
-            ref_rope(c->q, m->n_head, hd, m->n_rot, pos, m->rope_freq_base, 2);
+            ref_rope_ext(c->q, m->n_head, hd, m->n_rot, pos, m->rope_freq_base, 2, m->rope_freq_scale, m->rope_factors);
             const float qs = 1.0f / sqrtf((float)hd);
             for (size_t i = 0; i < qdim; i++) c->q[i] *= qs;        /* q pre-scaled, kq_scale = 1 */
-            ref_rope(c->k, m->n_head_kv, hd, m->n_rot, pos, m->rope_freq_base, 2);
+            ref_rope_ext(c->k, m->n_head_kv, hd, m->n_rot, pos, m->rope_freq_base, 2, m->rope_freq_scale, m->rope_factors);
             store_kv(c, il, pos);
             attend(c, il, pos, 1.0f);
             matvec(c, &L->wo, E, qdim, c->att, c->proj);

@@ -80,6 +80,8 @@ void ref_layer_norm(const float *x, const float *g, const float *b, float *y, in
 /* mode 0: adjacent pairs (llama "norm" rope); mode 2: NeoX halves. in place on
  * n_head vectors of head_dim; rotates the first n_rot dims. */
 void ref_rope(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode);
+/* the same with ggml's frequency factors and linear position scaling: theta = freq_scale * (theta_base / factor[pair]) */
+void ref_rope_ext(float *x, int n_head, int head_dim, int n_rot, int pos, float freq_base, int mode, float freq_scale, const float *factors);
 void ref_softmax(float *x, int64_t n);
 /* canonical-mode attention of one token (see ggml_ref.c); k, v: [n][n_head_kv*hd] f16 */
 void ref_attention_canon(const float *q, const uint16_t *k, const uint16_t *v, int n, int n_head, int n_head_kv, int hd, float scale, float *out);
@@ -107,6 +109,8 @@ typedef struct {
     float norm_eps, rope_freq_base;
     ref_tensor tok_embd, out_norm, out_norm_b, output, output_b;
     const ref_layer *layers;
+    float rope_freq_scale;        /* 1 / rope.scaling.factor for linear scaling, else 1 (0 is read as 1) */
+    const float *rope_factors;    /* rope_freqs.weight [n_rot/2] or NULL: theta is divided by it per pair */
 } ref_model;
 
 typedef struct ref_ctx ref_ctx;   /* KV cache (f16 when faithful, f32 when ideal) + scratch */

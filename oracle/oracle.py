@@ -41,7 +41,7 @@ class Model(C.Structure):
         "n_layer", "n_embd", "n_head", "n_head_kv", "head_dim", "n_ff", "n_vocab", "n_ctx", "n_rot")] + [
         ("norm_eps", C.c_float), ("rope_freq_base", C.c_float),
         ("tok_embd", Tensor), ("out_norm", Tensor), ("out_norm_b", Tensor), ("output", Tensor), ("output_b", Tensor),
-        ("layers", C.POINTER(Layer))]
+        ("layers", C.POINTER(Layer)), ("rope_freq_scale", C.c_float), ("rope_factors", C.c_void_p)]
 
 
 _lib = None
@@ -68,6 +68,7 @@ def lib() -> C.CDLL:
         L.ref_rms_norm.argtypes = [vp, vp, vp, i64, C.c_float]
         L.ref_layer_norm.argtypes = [vp, vp, vp, vp, i64, C.c_float]
         L.ref_rope.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]
+        L.ref_rope_ext.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, vp]
         L.ref_softmax.argtypes = [vp, i64]
         L.ref_attention_canon.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]
         L.ref_ctx_new.restype = vp
@@ -134,6 +135,13 @@ def rope(x, n_head, head_dim, n_rot, pos, freq_base, mode):
     return x
 
 
+def rope_ext(x, n_head, head_dim, n_rot, pos, freq_base, mode, freq_scale=1.0, factors=None):
+    x = np.ascontiguousarray(x, dtype=np.float32).copy()
+    f = None if factors is None else np.ascontiguousarray(factors, dtype=np.float32)
+    lib().ref_rope_ext(_p(x), n_head, head_dim, n_rot, pos, freq_base, mode, freq_scale, _p(f) if f is not None else None)
+    return x
+
+
 def attention_canon(q, k, v, n_head, n_head_kv, hd, scale):
     """Canonical-mode attention of one token: q f32 [n_head*hd], k / v f16 [n][n_head_kv*hd]."""
     q = np.ascontiguousarray(q, np.float32); k = np.ascontiguousarray(k, np.float16); v = np.ascontiguousarray(v, np.float16)
@@ -174,6 +182,16 @@ class OracleModel:
         m.rope_freq_base = kv(f"{arch}.rope.freq_base", 10000.0)
         m.n_vocab = int(self.tensors["token_embd.weight"].shape[1])
         self._keep = []
+        # rope.scaling.type: 0 none, 1 linear, 2 yarn (gguf.RopeScalingType); stored as a string
+        st = kv(f"{arch}.rope.scaling.type", "none")
+        if st not in ("none", "linear"):
+            raise NotImplementedError(f"rope scaling type {st}")
+        m.rope_freq_scale = 1.0 / float(kv(f"{arch}.rope.scaling.factor", 1.0)) if st == "linear" else 1.0
+        rf = self.tensors.get("rope_freqs.weight")
+        if rf is not None:
+            a = np.ascontiguousarray(rf.data, dtype=np.float32)
+            self._keep.append(a)
+            m.rope_factors = a.ctypes.data
 
         def T(name, optional=False):
             t = self.tensors.get(name)

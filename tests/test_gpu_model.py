@@ -47,7 +47,7 @@ def _teacher_forced_compare(pkg, oracle, eng, path, n_prompt, n_steps, flags=0, 
     return worst, n_same
 
 
-@pytest.mark.parametrize("preset", ["tiny-llama", "tiny-gqa", "tiny-phi2", "tiny-gqa8", "tiny-phi2-80"])
+@pytest.mark.parametrize("preset", ["tiny-llama", "tiny-gqa", "tiny-phi2", "tiny-gqa8", "tiny-phi2-80", "tiny-rope31"])
 def test_logits_match_oracle(pkg, oracle, eng, model_dir, preset):
     path = pkg.synth.cached_model(preset, model_dir)
     worst, n_same = _teacher_forced_compare(pkg, oracle, eng, path, 9, 40)

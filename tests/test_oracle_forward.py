@@ -117,3 +117,24 @@ def test_eval_rejects_bad_token_and_position(oracle, pkg, model_dir):
         om.eval(om.m.n_vocab)
     with pytest.raises(ValueError):
         om.eval(0, pos=om.m.n_ctx)
+
+
+def test_rope_factors_and_linear_scaling(oracle, pkg, model_dir):
+    """ggml's rope with `rope_freqs.weight` and `rope.scaling.type = linear` (Llama-3.1 files): the angle of pair p at
+    position pos is freq_scale * pos * base^(-2p/n_rot) / factor[p]; checked against a float64 restatement, and the
+    synthetic Llama-3.1-style model must differ from the same weights read without the two settings."""
+    rng = np.random.default_rng(5)
+    hd, n_rot, pos, base = 64, 64, 37, 500000.0
+    x = rng.standard_normal((2, hd)).astype(np.float32)
+    fac = np.linspace(1.0, 8.0, n_rot // 2).astype(np.float32)
+    got = oracle.rope_ext(x, 2, hd, n_rot, pos, base, 0, 0.25, fac)
+    p = np.arange(n_rot // 2)
+    th = 0.25 * pos * base ** (-2.0 * p / n_rot) / fac.astype(np.float64)
+    want = x.astype(np.float64).copy()
+    want[:, 0::2] = x[:, 0::2] * np.cos(th) - x[:, 1::2] * np.sin(th)
+    want[:, 1::2] = x[:, 0::2] * np.sin(th) + x[:, 1::2] * np.cos(th)
+    assert np.max(np.abs(got - want)) < 2e-4
+    plain = oracle.rope_ext(x, 2, hd, n_rot, pos, base, 0)
+    assert np.max(np.abs(plain - got)) > 1e-2
+    om = oracle.OracleModel(pkg.synth.cached_model("tiny-rope31", model_dir))
+    assert abs(om.m.rope_freq_scale - 0.25) < 1e-7 and om.m.rope_factors

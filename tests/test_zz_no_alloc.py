@@ -48,3 +48,30 @@ def test_requests_beyond_the_static_scratch_are_refused(pkg):
     # the refusal did no partial work: the next valid call is still right
     W2, x2, _ = _case(pkg, E.TYPE_Q4_0, 64, 512, 3, False)
     assert np.array_equal(E.gemv_noalloc(E.TYPE_Q4_0, W2, 64, 512, x2), E.gemv(E.TYPE_Q4_0, W2, 64, 512, x2))
+
+
+def test_calls_leave_free_device_memory_unchanged(pkg):
+    """The point of the entry: no device allocation.  After one call that has done the once-per-device
+    set-up, further calls must leave cudaMemGetInfo's free byte count exactly where it was."""
+    import torch
+    E = pkg.engine
+    W, x, g = _case(pkg, E.TYPE_Q4_0, 512, 2048, 4, True)
+    E.gemv_noalloc(E.TYPE_Q4_0, W, 512, 2048, x, gain=g, eps=1e-5)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(3):
+        E.gemv_noalloc(E.TYPE_Q4_0, W, 512, 2048, x, gain=g, eps=1e-5)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, (free0, free1)
+
+
+def test_absurd_sizes_are_refused_before_any_arithmetic_can_wrap(pkg):
+    E = pkg.engine
+    lib = E.lib()
+    y = np.zeros(4, np.float32)
+    W = np.zeros(64, np.uint8)
+    x = np.zeros(32, np.float32)
+    # rows * row_bytes would wrap a 64-bit size to something small; the bound on rows alone must catch it
+    rc = lib.b2_gemv_noalloc(E.TYPE_Q4_0, W.ctypes.data, 2 ** 60, 32, x.ctypes.data, None, 0.0, y.ctypes.data)
+    assert rc == -6, rc
