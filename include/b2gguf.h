@@ -152,6 +152,12 @@ int b2_gemv_noalloc(int ggml_type, const void* W, int64_t rows, int64_t k, const
  * b2_gemv on that column bit for bit.  The kernel runs `iters` more times for *ms_out (may be NULL). */
 int b2_gemm(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, int n_cols, const float* gain, float eps, float* y, int iters,
             float* ms_out);
+/* The same product on the tcgen05 tensor cores (integer MMA per 32-weight block, accumulators in tensor memory),
+ * n_cols 1..128: the kernel behind chunked b2_prefill and batched b2_decode for Q4_0 matrices whose k is a multiple of
+ * 256.  acc32 = 0: block terms added in f64 (every column equals b2_gemv bit for bit); acc32 = 1: f32, block after
+ * block, the order of ggml's generic C kernel (ggml-quants.c ggml_vec_dot_q4_0_q8_0, scalar branch [upstream]). */
+int b2_gemm_tc(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, int n_cols, const float* gain, float eps, int acc32, float* y, int iters,
+               float* ms_out);
 /* Same kernel launched `iters` times back to back on resident data; returns the mean device
  * time per launch in *ms_out (CUDA events).  tune = {nb, g, rpg, ns, ctas_per_sm}, zeros for
  * the built-in heuristic. */

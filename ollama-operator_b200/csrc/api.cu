@@ -482,4 +482,48 @@ int b2_gemm(int ggml_type, const void* W, int64_t rows, int64_t k, const float* 
     return B2_OK;
 }
 
+int b2_gemm_tc(int ggml_type, const void* W, int64_t rows, int64_t k, const float* x, int n_cols, const float* gain, float eps, int acc32, float* y, int iters,
+               float* ms_out) {
+    if (!W || !x || !y || n_cols < 1 || n_cols > TC_COLS_MAX) B2_FAIL(B2_ERR_ARG, "b2_gemm_tc: bad arguments (1..%d columns)", TC_COLS_MAX);
+    B2_TRY(check_quant_shape(ggml_type, rows, k));
+    B2_TRY(check_device());
+    const size_t nbytes = (size_t)rows * type_row_bytes(ggml_type, k);
+    DevBuf src, dx, dg, dy, planes[4], dq, dd, dargs, dpos, dpt;
+    QMat m;
+    B2_TRY(src.alloc(nbytes)); B2_TRY(dx.alloc((size_t)n_cols * k * 4)); B2_TRY(dg.alloc((size_t)k * 4)); B2_TRY(dy.alloc((size_t)n_cols * rows * 4));
+    B2_TRY(alloc_qmat(m, planes, ggml_type, rows, k));
+    if (!gemm_tc_supported(m)) B2_FAIL(B2_ERR_UNSUPPORTED, "b2_gemm_tc: Q4_0 with k a multiple of 256 and an even row count only");
+    B2_TRY(dq.alloc((size_t)TC_COLS_MAX * k)); B2_TRY(dd.alloc((size_t)(k / 32) * TC_COLS_MAX * 4));
+    B2_CUDA(cudaMemset(dq.p, 0, (size_t)TC_COLS_MAX * k)); B2_CUDA(cudaMemset(dd.p, 0, (size_t)(k / 32) * TC_COLS_MAX * 4));
+    B2_TRY(dargs.alloc(sizeof(GemvArgs) * TC_COLS_MAX)); B2_TRY(dpos.alloc(TC_COLS_MAX * 4)); B2_TRY(dpt.alloc(TC_COLS_MAX * 4));
+    B2_CUDA(cudaMemset(dpos.p, 0, TC_COLS_MAX * 4)); B2_CUDA(cudaMemset(dpt.p, 0, TC_COLS_MAX * 4));
+    B2_CUDA(cudaMemcpy(src.p, W, nbytes, cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(dx.p, x, (size_t)n_cols * k * 4, cudaMemcpyHostToDevice));
+    if (gain) B2_CUDA(cudaMemcpy(dg.p, gain, (size_t)k * 4, cudaMemcpyHostToDevice));
+    B2_TRY(repack(ggml_type, src.p, rows, k, m, 0, 1, 0));
+    TcMaps maps;
+    B2_TRY(gemm_tc_make_maps(m, &maps));
+    TcCols cols;
+    B2_TRY(tc_cols_init(cols, dq.as<int8_t>(), dd.as<float>(), k, TC_COLS_MAX));
+    std::vector<GemvArgs> ca(n_cols);
+    for (int c = 0; c < n_cols; c++) { ca[c].epi = EPI_STORE; ca[c].y = dy.as<float>() + (size_t)c * rows; }
+    B2_CUDA(cudaMemcpy(dargs.p, ca.data(), sizeof(GemvArgs) * n_cols, cudaMemcpyHostToDevice));
+    B2_TRY(quant_cols_tc_launch(dx.as<float>(), k, k, n_cols, gain ? PRO_RMSNORM : PRO_PLAIN, dg.as<float>(), nullptr, eps, cols, 0));
+    cudaEvent_t e0, e1;
+    B2_CUDA(cudaEventCreate(&e0)); B2_CUDA(cudaEventCreate(&e1));
+    const int n = iters > 0 ? iters : 1;
+    B2_TRY(gemm_tc_launch(m, maps, cols, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0, false, acc32 != 0));
+    B2_CUDA(cudaDeviceSynchronize());
+    cudaEventRecord(e0, 0);
+    for (int i = 0; i < n; i++) B2_TRY(gemm_tc_launch(m, maps, cols, n_cols, dargs.as<GemvArgs>(), dpos.as<int>(), dpt.as<int>(), 1, 0, false, acc32 != 0));
+    cudaEventRecord(e1, 0);
+    B2_CUDA(cudaDeviceSynchronize());
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms_out) *ms_out = ms / n;
+    B2_CUDA(cudaMemcpy(y, dy.p, (size_t)n_cols * rows * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+
 }  // extern "C"

@@ -198,6 +198,23 @@ int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B
                      cudaStream_t st, bool partial_out = false);      // partial_out: the columns' epilogue is EPI_PARTIAL
 // attention for B columns: d_args[c] describes column c (q, out, page table, position pointer)
 int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& shape, int B, cudaStream_t st);
+// ---- gemm_tc.cu: the same product on tcgen05 tensor cores (kind::i8, TMEM accumulators), up to 128 columns per pass ----
+constexpr int TC_COLS_MAX = 128;
+struct alignas(64) TcMaps { CUtensorMap q, d; };      // TMA descriptors of one Q4_0 matrix: nibble plane (swizzled 128 x 128 B boxes), scale plane
+struct alignas(64) TcCols {                           // Q8_0-quantised activation columns, K-major: q [cols_cap][k_cap] s8, d [k_cap / 32][cols_cap] f32
+    CUtensorMap map32, map64, map128;                 // boxes of 32 / 64 / 128 columns x 128 bytes of K, 128-byte swizzle
+    int8_t* q = nullptr;
+    float* d = nullptr;
+    int64_t k_cap = 0;
+    int cols_cap = 0;
+};
+bool gemm_tc_supported(const QMat& W);
+int gemm_tc_make_maps(const QMat& W, TcMaps* out);
+int tc_cols_init(TcCols& c, int8_t* q, float* d, int64_t k_cap, int cols_cap);
+int quant_cols_tc_launch(const float* x, int64_t x_stride, int64_t K, int B, int pro, const float* gain, const float* nbias, float eps, const TcCols& out,
+                         cudaStream_t st);
+int gemm_tc_launch(const QMat& W, const TcMaps& maps, const TcCols& x, int B, const GemvArgs* d_colargs, const int* d_pos, const int* d_pt, int pt_stride,
+                   cudaStream_t st, bool partial_out = false, bool acc32 = false);
 // next token of every column from its arg-max accumulator
 int batch_end_launch(const unsigned long long* keys, int* d_next, int B, cudaStream_t st);
 }  // namespace b2

@@ -22,7 +22,7 @@ LOAD_NO_PDL, LOAD_NO_GRAPH, LOAD_NO_MEGA, LOAD_NO_BATCH = 1, 2, 4, 8
 SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
     "b2_seq_new", "b2_seq_assume", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
-    "b2_get_stats", "b2_mega_trace", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemm", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
+    "b2_get_stats", "b2_mega_trace", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemm", "b2_gemm_tc", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
 ]
 
 
@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
         L.b2_dequantize_repacked.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp]
         L.b2_gemv.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp, vp, C.c_float, vp]
         L.b2_gemm.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp, C.c_int, vp, C.c_float, vp, C.c_int, fp]
+        L.b2_gemm_tc.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp, C.c_int, vp, C.c_float, C.c_int, vp, C.c_int, fp]
         L.b2_gemv_noalloc.argtypes = [C.c_int, vp, C.c_int64, C.c_int64, vp, vp, C.c_float, vp]
         L.b2_gemv_bench.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int, vp, fp]
         L.b2_attn_decode.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp]
@@ -134,6 +135,19 @@ def gemm(ggml_type: int, W: np.ndarray, rows: int, k: int, x: np.ndarray, gain: 
     y = np.empty((x.shape[0], rows), dtype=np.float32)
     ms = C.c_float(0)
     _check(lib().b2_gemm(ggml_type, _ptr(W), rows, k, _ptr(x), x.shape[0], _ptr(g), eps, _ptr(y), iters, C.byref(ms)))
+    return y, ms.value
+
+
+def gemm_tc(ggml_type: int, W: np.ndarray, rows: int, k: int, x: np.ndarray, gain: np.ndarray | None = None, eps: float = 0.0, acc32: bool = False,
+            iters: int = 0):
+    """The batched product on the tcgen05 tensor cores: x [n_cols <= 128][k] -> y [n_cols][rows]; returns (y, ms per launch).
+    acc32: ggml's generic f32 accumulation order instead of the canonical f64 one."""
+    W = np.ascontiguousarray(W, dtype=np.uint8)
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, k)
+    g = None if gain is None else np.ascontiguousarray(gain, dtype=np.float32)
+    y = np.empty((x.shape[0], rows), dtype=np.float32)
+    ms = C.c_float(0)
+    _check(lib().b2_gemm_tc(ggml_type, _ptr(W), rows, k, _ptr(x), x.shape[0], _ptr(g), eps, int(acc32), _ptr(y), iters, C.byref(ms)))
     return y, ms.value
 
 
