@@ -40,7 +40,7 @@ __global__ void batch_begin_kernel(QMat embd, float* xb, int64_t x_stride, const
 }
 
 __global__ void batch_end_kernel(const unsigned long long* keys, int* next, int B) {
-    const int c = threadIdx.x;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < B) next[c] = (int)(0xFFFFFFFFu - (uint32_t)(keys[c] & 0xFFFFFFFFull));
 }
 
@@ -75,7 +75,7 @@ int batch_begin_launch(const QMat& embd, float* xb, int64_t x_stride, const int*
     return B2_OK;
 }
 int batch_end_launch(const unsigned long long* keys, int* d_next, int B, cudaStream_t st) {
-    batch_end_kernel<<<1, 32, 0, st>>>(keys, d_next, B);
+    batch_end_kernel<<<(B + 127) / 128, 128, 0, st>>>(keys, d_next, B);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
 }

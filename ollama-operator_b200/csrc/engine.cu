@@ -779,17 +779,19 @@ int Model::prefill(int seq, const int32_t* toks, int n, float* logits) {
     B2_TRY(ensure_pages(s, s.len + n));
     B2_TRY(begin_call());
     if (bt.ok && n >= batch_min_seqs) {
-        // chunks of up to BATCH_MAX prompt tokens per pass over the weights; only the last token needs the head
+        // chunks of up to bt.cap prompt tokens per pass over the weights (512 on the tensor-core path, else 32); only the
+        // last token needs the head
         bt.next_region = 0;
-        int col_slot[BATCH_MAX], col_pos[BATCH_MAX], last_b = 0;
-        for (int t0 = 0; t0 < n; t0 += BATCH_MAX) {
-            const int B = std::min(BATCH_MAX, n - t0);
+        std::vector<int> col_slot(bt.cap), col_pos(bt.cap);
+        int last_b = 0;
+        for (int t0 = 0; t0 < n; t0 += bt.cap) {
+            const int B = std::min(bt.cap, n - t0);
             for (int c = 0; c < B; c++) { col_slot[c] = seq; col_pos[c] = s.len + t0 + c; }
-            B2_TRY(batch_step(B, col_slot, col_pos, toks + t0, t0 + B == n ? 1u << (B - 1) : 0u));
+            B2_TRY(batch_step(B, col_slot.data(), col_pos.data(), toks + t0, t0 + B == n ? B - 1 : B));
             last_b = B;
         }
-        if (logits) B2_CUDA(cudaMemcpyAsync(logits, bt.logits + (size_t)(last_b - 1) * hp.n_vocab, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
-        B2_CUDA(cudaMemcpyAsync(bt.h_next, bt.d_next, BATCH_MAX * 4, cudaMemcpyDeviceToHost, stream));
+        if (logits) B2_CUDA(cudaMemcpyAsync(logits, bt.logits, (size_t)hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
+        B2_CUDA(cudaMemcpyAsync(bt.h_next, bt.d_next, (size_t)last_b * 4, cudaMemcpyDeviceToHost, stream));
         B2_TRY(end_call(nullptr));
         s.host = SeqState{};
         s.host.cur_tok = bt.h_next[last_b - 1];
@@ -826,7 +828,7 @@ int Model::decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* 
         for (int c0 = 0; c0 < n_seq; c0 += BATCH_MAX) {
             const int B = std::min(BATCH_MAX, n_seq - c0);
             for (int c = 0; c < B; c++) col_pos[c] = slots[seqs[c0 + c]].len;
-            B2_TRY(batch_step(B, seqs + c0, col_pos, last_tok + c0, B == 32 ? 0xFFFFFFFFu : (1u << B) - 1));
+            B2_TRY(batch_step(B, seqs + c0, col_pos, last_tok + c0, 0));
             if (logits) B2_CUDA(cudaMemcpyAsync(logits + (size_t)c0 * hp.n_vocab, bt.logits, (size_t)B * hp.n_vocab * 4, cudaMemcpyDeviceToHost, stream));
             B2_CUDA(cudaMemcpyAsync(bt.h_next, bt.d_next, BATCH_MAX * 4, cudaMemcpyDeviceToHost, stream));
             {

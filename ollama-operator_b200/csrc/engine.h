@@ -68,6 +68,11 @@ struct BatchCtx {
     void* mem = nullptr;
     float *x = nullptr, *q = nullptr, *att = nullptr, *att2 = nullptr, *h = nullptr, *logits = nullptr;   // [BATCH_MAX][...]
     Q8Cols q8;
+    int cap = BATCH_MAX;             // columns per step the buffers hold: BATCH_MAX, or TC_COLS_MAX when the tensor-core path serves the model
+    bool tc_ok = false;              // chunks of more than BATCH_MAX columns go through gemm_tc.cu (tcgen05)
+    bool tc_acc32 = false;           // ... with ggml's generic f32 accumulation order instead of the canonical f64 one
+    TcCols tc;
+    std::vector<TcMaps> tcmaps;
     int *d_tok = nullptr, *d_pos = nullptr, *d_pt = nullptr, *d_next = nullptr;    // d_pt: [BATCH_MAX][pages_per_seq]
     unsigned long long* d_keys = nullptr;
     GemvArgs* d_colargs = nullptr;   // [ops][BATCH_MAX]
@@ -139,7 +144,7 @@ struct Model {
     int enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* prof);
     int run_steps(Slot& s, bool with_head, int n);
     int setup_batch();
-    int batch_step(int B, const int* col_slot, const int* col_pos, const int32_t* col_tok, uint32_t head_mask);
+    int batch_step(int B, const int* col_slot, const int* col_pos, const int32_t* col_tok, int head_from);
     int begin_call();
     int end_call(Slot* s);
 };

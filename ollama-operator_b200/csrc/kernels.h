@@ -199,7 +199,7 @@ int gemm_w4a8_launch(const QMat& W, const GemmMaps& maps, const Q8Cols& x, int B
 // attention for B columns: d_args[c] describes column c (q, out, page table, position pointer)
 int attn_decode_batch_launch(const AttnArgs* d_args, const AttnArgs& shape, int B, cudaStream_t st);
 // ---- gemm_tc.cu: the same product on tcgen05 tensor cores (kind::i8, TMEM accumulators), up to 128 columns per pass ----
-constexpr int TC_COLS_MAX = 128;
+constexpr int TC_COLS_MAX = 512;      // columns of one pass (a prompt chunk); a CTA takes 32, 64 or 128 of them
 struct alignas(64) TcMaps { CUtensorMap q, d; };      // TMA descriptors of one Q4_0 matrix: nibble plane (swizzled 128 x 128 B boxes), scale plane
 struct alignas(64) TcCols {                           // Q8_0-quantised activation columns, K-major: q [cols_cap][k_cap] s8, d [k_cap / 32][cols_cap] f32
     CUtensorMap map32, map64, map128;                 // boxes of 32 / 64 / 128 columns x 128 bytes of K, 128-byte swizzle

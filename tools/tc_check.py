@@ -24,7 +24,7 @@ if "--time" in sys.argv:
     for name, rows, k in [("qkv", 12288, 4096), ("wo", 4096, 4096), ("gate|up", 22016, 4096), ("down", 4096, 11008)]:
         rng = np.random.default_rng(1)
         W = p.synth.random_blocks(T.Q4_0, rows, k, k ** -0.5, rng)
-        for n in (32, 64, 128):
+        for n in (32, 128, 512):
             x = rng.standard_normal((n, k)).astype(np.float32)
             for acc32 in (False, True):
                 _, ms = E.gemm_tc(E.TYPE_Q4_0, W, rows, k, x, acc32=acc32, iters=20)
