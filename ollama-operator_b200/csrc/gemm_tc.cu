@@ -42,13 +42,15 @@ using namespace gemvdev;
 
 constexpr int TC_M = 128;                 // weight rows per CTA
 constexpr int TC_KC = 8;                  // 32-weight blocks per K chunk (256 weights = two 128-byte atoms of s8)
-constexpr int TC_NS = 2;                  // pipeline stages
-constexpr int TC_UNPACK_WARPS = 4;
+constexpr int TC_NS = 3;                  // pipeline stages
+constexpr int TC_NB = 8;                  // accumulator buffers in tensor memory: the MMAs run up to eight blocks ahead of the drain
+constexpr int TC_UNPACK_WARPS = 2;             // each thread unpacks two rows (12 warps in all leave the epilogue 168 registers)
 constexpr int TC_FIRST_EPI_WARP = 2 + TC_UNPACK_WARPS;
 
 template <int NT> struct TcCfg {
-    static constexpr int NEPI = NT >= 64 ? 8 : 4;                    // epilogue warps (4 TMEM lane quarters x column groups)
-    static constexpr int CPT = NT / (NEPI / 4);                      // accumulator columns per epilogue thread
+    static constexpr int NEPI = NT / 8;                              // epilogue warps: 4 TMEM lane quarters x (NT / 32) column groups
+    static constexpr int CPT = 32;                                   // accumulator columns per epilogue thread (one tcgen05.ld.32x32b.x32)
+    static_assert(NT == 32 || NT == 64, "column tile");
     static constexpr int THREADS = (TC_FIRST_EPI_WARP + NEPI) * 32;
     static constexpr int OFF_RAW = 0;                                // nibbles  [128 rows][128 B], swizzled
     static constexpr int OFF_A = OFF_RAW + TC_M * 128;               // s8 A     2 atoms x [128 rows][128 B]
@@ -57,8 +59,8 @@ template <int NT> struct TcCfg {
     static constexpr int OFF_DA = OFF_SC + TC_M * TC_KC * 2;         // f32 d_a  [8 blocks][NT]
     static constexpr int STAGE = (OFF_DA + TC_KC * NT * 4 + 1023) / 1024 * 1024;
     static constexpr int TX_BYTES = TC_M * 128 + 2 * NT * 128 + TC_M * TC_KC * 2 + TC_KC * NT * 4;
-    static constexpr int TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;      // two accumulator buffers
-    static constexpr size_t SMEM = 1024 + (size_t)TC_NS * STAGE + 256;
+    static constexpr int TMEM_COLS = TC_NB * NT;                     // 256 or 512 columns (a power of two)
+    static constexpr size_t SMEM = 1024 + (size_t)TC_NS * STAGE + 512;
     static_assert(OFF_A % 1024 == 0 && OFF_B % 1024 == 0 && OFF_SC % 128 == 0 && OFF_DA % 16 == 0, "stage layout alignment");
     static_assert((size_t)TC_M * (NT + 1) * 8 <= (size_t)TC_NS * STAGE, "output staging reuses the pipeline stages");
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
@@ -98,7 +100,17 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, int (&r)[32]) {
         : "r"(taddr)
         : "memory");
 }
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// Wait for this thread's outstanding tcgen05.ld.  The loaded registers are passed through as in/out operands so that
+// the compiler cannot schedule a use of them above the wait (the load is asynchronous until here).
+__device__ __forceinline__ void tc_wait_ld(int (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]),
+                   "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]),
+                   "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]),
+                   "+r"(r[31])
+                 :
+                 : "memory");
+}
 
 // Shared-memory matrix descriptor of a K-major operand in the 128-byte swizzled layout: rows of 128 bytes,
 // groups of 8 rows 1024 bytes apart (stride byte offset), descriptor version 1 (sm_100), layout type 2.
@@ -125,14 +137,14 @@ template <int NT, bool ACC64>
 __global__ void __launch_bounds__(TcCfg<NT>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUtensorMap xmap, const float* __restrict__ xd, const int xd_stride,
                const int rows, const int nbk, const int B, const GemvArgs* __restrict__ colargs, const int* __restrict__ col_pos,
-               const int* __restrict__ col_pt, const int pt_stride) {
+               const int* __restrict__ col_pt, const int pt_stride, const int debug) {
     using C = TcCfg<NT>;
     using acc_t = typename std::conditional<ACC64, double, float>::type;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);      // swizzled operands need 1024-byte alignment
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)TC_NS * C::STAGE);
-    uint64_t *full = bars, *aready = bars + 2, *sfree = bars + 4, *dfull = bars + 6, *dfree = bars + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+    uint64_t *full = bars, *aready = bars + TC_NS, *sfree = bars + 2 * TC_NS, *dfull = bars + 3 * TC_NS, *dfree = bars + 3 * TC_NS + TC_NB;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * TC_NS + 2 * TC_NB);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int row0 = blockIdx.x * TC_M, col0 = blockIdx.y * NT;
@@ -144,8 +156,10 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
             mbar_init(&full[s], 1);
             mbar_init(&aready[s], TC_UNPACK_WARPS);
             mbar_init(&sfree[s], 1 + C::NEPI);
-            mbar_init(&dfull[s], 1);
-            mbar_init(&dfree[s], C::NEPI);
+        }
+        for (int i = 0; i < TC_NB; i++) {
+            mbar_init(&dfull[i], 1);
+            mbar_init(&dfree[i], C::NEPI);
         }
         mbar_fence_init();
     }
@@ -166,7 +180,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
             auto issue_w = [&](int it) {
                 const int s = it % TC_NS;
                 uint8_t* st = smem + (size_t)s * C::STAGE;
-                mbar_expect_tx(&full[s], C::TX_BYTES);
+                mbar_expect_tx(&full[s], (debug & 8) ? C::TX_BYTES - TC_KC * NT * 4 : C::TX_BYTES);
                 tma_box_2d(st + C::OFF_RAW, &wmaps.q, it * (TC_KC * 16), row0, &full[s], pol_w);
                 tma_box_2d(st + C::OFF_SC, &wmaps.d, it * (TC_KC * 2), row0, &full[s], pol_w);
             };
@@ -175,6 +189,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
                 uint8_t* st = smem + (size_t)s * C::STAGE;
                 tma_box_2d(st + C::OFF_B, &xmap, it * (TC_KC * 32), col0, &full[s], pol_x);
                 tma_box_2d(st + C::OFF_B + NT * 128, &xmap, it * (TC_KC * 32) + 128, col0, &full[s], pol_x);
+                if (!(debug & 8))
 #pragma unroll
                 for (int b = 0; b < TC_KC; b++)
                     bulk_g2s(st + C::OFF_DA + b * NT * 4, xd + (size_t)(it * TC_KC + b) * xd_stride + col0, NT * 4, &full[s], pol_x);
@@ -203,11 +218,12 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
                 const uint32_t a_base = smem_u32(smem + (size_t)s * C::STAGE + C::OFF_A), b_base = smem_u32(smem + (size_t)s * C::STAGE + C::OFF_B);
 #pragma unroll
                 for (int b = 0; b < TC_KC; b++) {
-                    const int g = it * TC_KC + b, buf = g & 1;
-                    if (g >= 2) { mbar_wait_bounded(&dfree[buf], ((g >> 1) - 1) & 1); tc_fence_after(); }
+                    const int g = it * TC_KC + b, buf = g % TC_NB;
+                    if (g >= TC_NB && !(debug & 32)) { mbar_wait_bounded(&dfree[buf], ((g / TC_NB) - 1) & 1); tc_fence_after(); }
                     const uint64_t ad = tc_desc_sw128(a_base + (b >> 2) * (TC_M * 128) + (b & 3) * 32);
                     const uint64_t bd = tc_desc_sw128(b_base + (b >> 2) * (NT * 128) + (b & 3) * 32);
                     tc_mma_i8(tmem_base + buf * NT, ad, bd, idesc);
+                    if (debug & 16) { tc_mma_i8(tmem_base + buf * NT, ad, bd, idesc); tc_mma_i8(tmem_base + buf * NT, ad, bd, idesc); tc_mma_i8(tmem_base + buf * NT, ad, bd, idesc); }
                     tc_commit(&dfull[buf]);
                 }
                 tc_commit(&sfree[s]);                       // this stage's operands are no longer read by the tensor core
@@ -215,11 +231,14 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
         }
     } else if (warp < TC_FIRST_EPI_WARP) {
         // ===== unpack: nibbles -> signed bytes in the UMMA operand layout =====
-        const int r = (warp - 2) * 32 + lane, r7 = r & 7;
-        const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)r7 * 128u;
         for (int it = 0; it < n_chunks; it++) {
             const int s = it % TC_NS;
             mbar_wait_bounded(&full[s], (it / TC_NS) & 1);
+          if (!(debug & 4))
+#pragma unroll
+          for (int rr = 0; rr < TC_M / (TC_UNPACK_WARPS * 32); rr++) {
+            const int r = rr * (TC_UNPACK_WARPS * 32) + (warp - 2) * 32 + lane, r7 = r & 7;
+            const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)r7 * 128u;
             const uint8_t* raw = smem + (size_t)s * C::STAGE + C::OFF_RAW + row_off;
             uint8_t* arow = smem + (size_t)s * C::STAGE + C::OFF_A + row_off;
 #pragma unroll
@@ -235,6 +254,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
                 *reinterpret_cast<uint4*>(atom + ((ch ^ r7) << 4)) = lo;
                 *reinterpret_cast<uint4*>(atom + (((ch + 1) ^ r7) << 4)) = hi;
             }
+          }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the tensor core's reads
             __syncwarp();
             if (lane == 0) mbar_arrive(&aready[s]);
@@ -249,44 +269,59 @@ gemm_tc_kernel(const __grid_constant__ TcMaps wmaps, const __grid_constant__ CUt
         acc_t acc[C::CPT];
 #pragma unroll
         for (int j = 0; j < C::CPT; j++) acc[j] = (acc_t)0;
-        for (int it = 0; it < n_chunks; it++) {
-            const int s = it % TC_NS;
-            mbar_wait_bounded(&full[s], (it / TC_NS) & 1);            // the scales of this chunk are in shared memory
-            const __half* sc = reinterpret_cast<const __half*>(smem + (size_t)s * C::STAGE + C::OFF_SC) + rl * TC_KC;
-            const float* da = reinterpret_cast<const float*>(smem + (size_t)s * C::STAGE + C::OFF_DA) + colbase;
-#pragma unroll 1
-            for (int b = 0; b < TC_KC; b++) {
-                const int g = it * TC_KC + b, buf = g & 1;
-                mbar_wait_bounded(&dfull[buf], (g >> 1) & 1);
-                tc_fence_after();
-                const float dw = __half2float(sc[b]);
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NT + colbase);
+        const int nblk = n_chunks * TC_KC;                              // even
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)colbase;
+        // scale the 32 block sums of block g (row rl, columns colbase..+31) and add them to the accumulators
+        auto accumulate = [&](const int (&v)[32], int g) {
+            const int s = (g / TC_KC) % TC_NS, b = g % TC_KC;
+            if (b == 0) mbar_wait_bounded(&full[s], ((g / TC_KC) / TC_NS) & 1);        // this chunk's scales are in shared memory
+            const float dw = __half2float(reinterpret_cast<const __half*>(smem + (size_t)s * C::STAGE + C::OFF_SC)[rl * TC_KC + b]);
+            const float* da = reinterpret_cast<const float*>(smem + (size_t)s * C::STAGE + C::OFF_DA) + b * NT + colbase;
+            if (!(debug & 1)) {
 #pragma unroll
-                for (int h = 0; h < C::CPT / 32; h++) {
-                    int v[32];
-                    tc_ld32(taddr + h * 32, v);
-                    tc_wait_ld();
-                    if (h == C::CPT / 32 - 1) {            // the buffer may be overwritten by the MMA after next
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&dfree[buf]);
-                    }
+            for (int j4 = 0; j4 < 8; j4++) {
+                const float4 d4 = *reinterpret_cast<const float4*>(da + j4 * 4);
+                const float dd[4] = {d4.x, d4.y, d4.z, d4.w};
 #pragma unroll
-                    for (int j4 = 0; j4 < 8; j4++) {
-                        const float4 d4 = *reinterpret_cast<const float4*>(da + b * NT + h * 32 + j4 * 4);
-                        const float dd[4] = {d4.x, d4.y, d4.z, d4.w};
-#pragma unroll
-                        for (int jj = 0; jj < 4; jj++) {
-                            const float t = __fmul_rn(__fmul_rn((float)v[j4 * 4 + jj], dw), dd[jj]);
-                            acc_t& a = acc[h * 32 + j4 * 4 + jj];
-                            if (ACC64) a += (acc_t)t;
-                            else a = (acc_t)__fadd_rn((float)a, t);
-                        }
-                    }
+                for (int jj = 0; jj < 4; jj++) {
+                    const float t = __fmul_rn(__fmul_rn((float)v[j4 * 4 + jj], dw), dd[jj]);
+                    acc_t& a = acc[j4 * 4 + jj];
+                    if (ACC64) a += (acc_t)t;
+                    else a = (acc_t)__fadd_rn((float)a, t);
                 }
             }
+            }
+            if (b == TC_KC - 1) {                                       // done with this stage's scales
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sfree[s]);
+            }
+        };
+        // The drain of block g + 1 (tcgen05.ld is asynchronous until tcgen05.wait::ld) runs under the arithmetic of block g:
+        // two register sets, two TMEM buffers, the loop unrolled by two so that both are static.
+        int vA[32], vB[32];
+        mbar_wait_bounded(&dfull[0], 0);
+        tc_fence_after();
+        tc_ld32(tbase, vA);
+        for (int g = 0; g < nblk; g += 2) {
+            const int b0 = g % TC_NB, b1 = (g + 1) % TC_NB, b2 = (g + 2) % TC_NB;
+            tc_wait_ld(vA);
+            tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sfree[s]);                     // done with this stage's scales
+            if (lane == 0) mbar_arrive(&dfree[b0]);                     // the buffer may take the MMA of block g + TC_NB
+            mbar_wait_bounded(&dfull[b1], ((g + 1) / TC_NB) & 1);
+            tc_fence_after();
+            if (!(debug & 2)) tc_ld32(tbase + b1 * NT, vB);
+            accumulate(vA, g);
+            tc_wait_ld(vB);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&dfree[b1]);
+            if (g + 2 < nblk) {
+                mbar_wait_bounded(&dfull[b2], ((g + 2) / TC_NB) & 1);
+                tc_fence_after();
+                if (!(debug & 2)) tc_ld32(tbase + b2 * NT, vA);
+            }
+            accumulate(vB, g + 1);
         }
         // ---- the GEMV epilogues: transpose through shared memory so that one thread holds a row pair of a column ----
         // (every stage has been consumed: all tensor-core reads and all TMA writes of this CTA are complete)
@@ -382,8 +417,9 @@ int gemm_tc_launch_t(const TcMaps& maps, const TcCols& x, int rows, int nbk, int
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = batch_pdl_enabled() ? 1 : 0;
-    const CUtensorMap& xm = NT == 128 ? x.map128 : NT == 64 ? x.map64 : x.map32;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, maps, xm, (const float*)x.d, x.cols_cap, rows, nbk, B, colargs, pos, pt, pt_stride));
+    const CUtensorMap& xm = NT == 64 ? x.map64 : x.map32;
+    static const int debug = getenv("B2_TC_DEBUG") ? atoi(getenv("B2_TC_DEBUG")) : 0;      // tuning experiments (results are wrong when set)
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, maps, xm, (const float*)x.d, x.cols_cap, rows, nbk, B, colargs, pos, pt, pt_stride, debug));
     return B2_OK;
 }
 
@@ -436,11 +472,10 @@ int gemm_tc_launch(const QMat& W, const TcMaps& maps, const TcCols& x, int B, co
     if (partial_out && acc32) B2_FAIL(B2_ERR_UNSUPPORTED, "gemm_tc: tensor-parallel partial sums need the f64 accumulation");
     const int rows = (int)W.rows, nbk = (int)(W.k / 32);
     if (acc32) {
-        if (B > 64 && x.cols_cap >= 128) return gemm_tc_launch_t<128, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
-        if (B > 32 && x.cols_cap >= 64) return gemm_tc_launch_t<64, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
+        if (B > 32) return gemm_tc_launch_t<64, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
         return gemm_tc_launch_t<32, false>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
     }
-    if (B > 32 && x.cols_cap >= 64) return gemm_tc_launch_t<64, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
+    if (B > 32) return gemm_tc_launch_t<64, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
     return gemm_tc_launch_t<32, true>(maps, x, rows, nbk, B, d_colargs, d_pos, d_pt, pt_stride, st);
 }
 

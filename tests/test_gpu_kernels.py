@@ -133,3 +133,34 @@ def test_batched_gemm_equals_gemv_per_column(pkg, oracle, rows, k, n_cols):
         assert np.array_equal(y[c].view(np.uint32), want.view(np.uint32)), (c, np.abs(y[c] - want).max())
         wn = oracle.mul_mat_vec(2, W, rows, k, oracle.rms_norm(x[c], g, 1e-5), faithful=2)
         assert np.array_equal(yn[c].view(np.uint32), wn.view(np.uint32)), c
+
+
+@pytest.mark.parametrize("rows,k,n_cols", [(128, 256, 1), (300, 512, 33), (1024, 4096, 64), (258, 11008, 17), (512, 4096, 128), (256, 1024, 512)])
+def test_tcgen05_gemm_matches_the_oracle_bit_for_bit(pkg, oracle, rows, k, n_cols):
+    """The tcgen05 / TMEM batched kernel (gemm_tc.cu): with f64 accumulation every column carries the bits of the
+    canonical oracle (and therefore of the GEMV); with f32 accumulation the bits of ggml's generic C order (oracle
+    mode 1: ggml_vec_dot_q4_0_q8_0, scalar branch) -- exact integer block sums either way."""
+    from gguf import GGMLQuantizationType as T
+    E = pkg.engine
+    rng = np.random.default_rng(rows + k + n_cols)
+    W = pkg.synth.random_blocks(T.Q4_0, rows, k, k ** -0.5, rng)
+    x = rng.standard_normal((n_cols, k)).astype(np.float32)
+    x[0, : k // 2] = 0
+    g = (1 + 0.02 * rng.standard_normal(k)).astype(np.float32)
+    y64, _ = E.gemm_tc(E.TYPE_Q4_0, W, rows, k, x)
+    y32, _ = E.gemm_tc(E.TYPE_Q4_0, W, rows, k, x, acc32=True)
+    yn, _ = E.gemm_tc(E.TYPE_Q4_0, W, rows, k, x, gain=g, eps=1e-5)
+    for c in range(0, n_cols, max(1, n_cols // 24)):
+        want = oracle.mul_mat_vec(2, W, rows, k, x[c], faithful=2)
+        assert np.array_equal(y64[c].view(np.uint32), want.view(np.uint32)), (c, np.abs(y64[c] - want).max())
+        w1 = oracle.mul_mat_vec(2, W, rows, k, x[c], faithful=1)
+        assert np.array_equal(y32[c].view(np.uint32), w1.view(np.uint32)), (c, np.abs(y32[c] - w1).max())
+        wn = oracle.mul_mat_vec(2, W, rows, k, oracle.rms_norm(x[c], g, 1e-5), faithful=2)
+        assert np.array_equal(yn[c].view(np.uint32), wn.view(np.uint32)), c
+
+
+def test_tcgen05_gemm_rejects_what_it_does_not_serve(pkg):
+    E = pkg.engine
+    W = np.zeros(64 * 320 // 32 * 18, np.uint8)
+    with pytest.raises(E.B2Error):
+        E.gemm_tc(E.TYPE_Q4_0, W, 64, 320, np.zeros((2, 320), np.float32))        # k not a multiple of 256

@@ -216,3 +216,25 @@ def test_cache_edges_and_prefix_reuse(pkg, eng, model_dir):
     with pytest.raises(E.B2Error):
         m.seq_len(s)
     m.close()
+
+
+def test_wide_model_long_prompt_through_the_tensor_core_path(pkg, oracle, eng, model_dir):
+    """SURVEY 8c (iv)/(v) at 7B width: a two-layer model with llama2-7B's matrix shapes.  A 200-token prompt goes
+    through the tcgen05 batched kernel in one chunk; its logits and the 64 greedy tokens that follow must be the
+    canonical oracle's, bit for bit -- and the same prompt evaluated token by token gives the same bits."""
+    path = pkg.synth.cached_model("wide-llama-2l", model_dir, source="blocks")
+    om = oracle.OracleModel(path, faithful=2)
+    m = eng.load(path, max_batch=1, max_ctx=300)
+    toks = pkg.synth.prompt_tokens(200, m.info.n_vocab)
+    seq = m.seq_new()
+    lg = m.prefill(seq, toks)
+    for t in toks:
+        want = om.eval(int(t))
+    assert np.array_equal(lg.view(np.uint32), want.view(np.uint32)), float(np.max(np.abs(lg - want)))
+    got = [int(np.argmax(lg))] + [int(t) for t in m.decode_greedy(seq, 63)]      # the loop continues from the prefill's arg-max
+    tok, ref = int(np.argmax(want)), []
+    for _ in range(64):
+        ref.append(tok)
+        tok = int(np.argmax(om.eval(tok)))
+    assert got == ref
+    m.close()

@@ -7,6 +7,14 @@ p = importlib.import_module("ollama-operator_b200"); import oracle
 from gguf import GGMLQuantizationType as T
 E = p.engine
 ok = True
+if "--one" in sys.argv:          # for ncu: one 7B qkv-shaped launch per accumulation mode, 512 columns
+    rng = np.random.default_rng(1)
+    W = p.synth.random_blocks(T.Q4_0, 12288, 4096, 4096 ** -0.5, rng)
+    x = rng.standard_normal((512, 4096)).astype(np.float32)
+    for acc32 in (False, True):
+        _, ms = E.gemm_tc(E.TYPE_Q4_0, W, 12288, 4096, x, acc32=acc32, iters=2)
+        print(f"qkv 12288x4096 x 512 columns acc32 {int(acc32)}: {ms * 1e3:.1f} us")
+    sys.exit(0)
 for rows, k, n in [(128, 256, 1), (128, 256, 32), (256, 512, 7), (300, 1024, 33), (1024, 4096, 64), (258, 11008, 17), (512, 4096, 128)]:
     rng = np.random.default_rng(rows + k + n)
     W = p.synth.random_blocks(T.Q4_0, rows, k, k ** -0.5, rng)
