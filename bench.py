@@ -199,7 +199,12 @@ def run_gpu(args):
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # rank 0 measures the tensor-parallel engine at the end while the others wait in a barrier: allow for a 70B load
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(minutes=40))
+        # a host-side group for the final rendezvous: an NCCL barrier would park a spinning kernel on every waiting rank's
+        # GPU, and the tensor-parallel engine rank 0 runs at the end needs those GPUs whole (cooperative launches)
+        host_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(minutes=40))
     p = pkg()
     cfg = p.synth.PRESETS[args.model]
     if rank == 0 or world == 1:
@@ -254,6 +259,9 @@ def run_gpu(args):
     if rank != 0:
         m.close(); eng.close()
         if dist:
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()
+            dist.barrier(group=host_group)      # rank 0 measures the tensor-parallel engine over all GPUs meanwhile (CPU-side wait)
             dist.destroy_process_group()
         return
 
@@ -315,9 +323,102 @@ def run_gpu(args):
     if world == 1 and not args.no_batch:
         out["batch32"] = batch_decode(args, p, eng, path, info)
     eng.close()
+    if not args.no_tp and os.environ.get("B2_BENCH_TP", "1") != "0":
+        # every other rank has released its engine (they returned above after the MAX of the timings); rank 0 now drives
+        # all of the job's GPUs itself -- the tensor-parallel engine is one process with one shard per GPU
+        try:
+            out["tp"] = tp_section(args, p, world)
+        except Exception as e:          # the replica headline above stands on its own
+            out["tp"] = {"error": f"{type(e).__name__}: {e}"}
     if dist:
+        dist.barrier(group=host_group)
         dist.destroy_process_group()
     print(json.dumps(out))
+
+
+def tp_run(p, path, tp, ctx, steps, n_batch, peak):
+    """One tensor-parallel engine (tp GPUs inside this process): greedy decode at a synthetic `ctx`-token context."""
+    E = p.engine
+    eng = E.Engine(list(range(tp)))
+    m = eng.load(path, max_batch=1 + n_batch, max_ctx=ctx + steps + 80, tp_size=tp)
+    info = m.info
+    s = m.seq_new()
+    m.seq_assume(s, ctx - 16)            # the cache rows are declared valid (zeros): reaching the context costs no prefill
+    m.prefill(s, p.synth.prompt_tokens(16, info.n_vocab))
+    m.decode_greedy(s, 4)
+    toks = m.decode_greedy(s, steps)
+    ms = m.stats().gpu_ms / steps
+    step_bytes = info.step_weight_bytes + (ctx + 4 + steps // 2) * info.kv_bytes_per_token
+    out = {"tp": tp, "tok_s": 1e3 / ms, "ms_per_step": ms, "per_gpu_hbm_frac": step_bytes / tp / (ms * 1e-3) / 1e9 / peak}
+    if n_batch > 1:
+        seqs = []
+        for i in range(n_batch):
+            q = m.seq_new(); m.seq_assume(q, ctx - 16); m.prefill(q, p.synth.prompt_tokens(16, info.n_vocab, seed=50 + i)); seqs.append(q)
+        tk = [1] * n_batch
+        for _ in range(2):
+            tk = [int(x) for x in m.decode(seqs, tk)]
+        g = []
+        for _ in range(6):
+            tk = [int(x) for x in m.decode(seqs, tk)]; g.append(m.stats().gpu_ms)
+        out["batch"] = {"n_seq": n_batch, "ms_per_step": float(np.median(g)), "tok_s": n_batch / float(np.median(g)) * 1e3, "tokens": tk}
+    m.close(); eng.close()
+    return out, [int(t) for t in toks]
+
+
+def tp_section(args, p, n):
+    """BASELINE.json configs 4-5 inside the driver's record: llama2-70B Q4_0 split over the job's n GPUs (one process,
+    one engine shard per GPU, exchange over NVLink peer memory), batch 1 and 16 sequences at a 2048-token context,
+    against the same model on one GPU; plus parity of the split models with their single-GPU bits and the oracle."""
+    peak, _ = peaks()
+    steps = int(os.environ.get("B2_TP_STEPS", "32"))
+    t0 = time.time()
+    path70 = p.synth.cached_model("llama2-70b", source="blocks")
+    gen_s = time.time() - t0
+    one, toks1 = tp_run(p, path70, 1, 2048, steps, 16 if n == 1 else 0, peak)
+    out = {"model": "llama2-70b Q4_0, decode at a 2048-token context (synthetic cache rows)", "steps": steps, "write_gguf_s": round(gen_s, 1), "tp1": one}
+    if n > 1:
+        run, toks = tp_run(p, path70, n, 2048, steps, 16, peak)
+        run["speedup_vs_tp1"] = run["tok_s"] / one["tok_s"]
+        run["tokens_equal_tp1"] = toks == toks1
+        out["tpN"] = run
+        out["tp_parity"] = tp_parity(p, n)
+    return out
+
+
+def tp_parity(p, n):
+    """The split model must give the single-GPU bits: logits of a prefill + 24 teacher-forced steps on a small GQA model
+    (8 query heads per KV head, as 70B) against tp = 1 and against the canonical oracle; 13B greedy tokens against tp = 1."""
+    E, o = p.engine, oracle_mod()
+    res = {}
+    path = p.synth.cached_model("tiny-gqa8")
+    toks = p.synth.prompt_tokens(9, p.synth.PRESETS["tiny-gqa8"].n_vocab)
+    tp = 2 if n >= 2 else 1           # tiny-gqa8 has two KV heads: at most two shards
+    logs = {}
+    for t in (1, tp):
+        eng = E.Engine(list(range(t))); m = eng.load(path, max_batch=1, max_ctx=128, tp_size=t)
+        s = m.seq_new(); lg = [m.prefill(s, toks)]
+        tok = int(np.argmax(lg[0]))
+        for _ in range(24):
+            nxt, l = m.decode([s], [tok], want_logits=True); lg.append(l[0]); tok = int(np.argmax(l[0]))
+        logs[t] = np.stack(lg); m.close(); eng.close()
+    om = o.OracleModel(path, faithful=2)
+    for t_ in toks:
+        w = om.eval(int(t_))
+    ref = [w]; tok = int(np.argmax(w))
+    for _ in range(24):
+        w = om.eval(tok); ref.append(w); tok = int(np.argmax(w))
+    ref = np.stack(ref)
+    res["tiny-gqa8"] = {"tp": tp, "logits_bits_equal_tp1": bool(np.array_equal(logs[tp].view(np.uint32), logs[1].view(np.uint32))),
+                        "tokens_equal_tp1": bool(np.array_equal(logs[tp].argmax(1), logs[1].argmax(1))),
+                        "oracle_max_abs": float(np.max(np.abs(logs[tp] - ref)))}
+    path13 = p.synth.cached_model("llama2-13b", source="blocks")
+    t13 = {}
+    for t in (1, n):
+        eng = E.Engine(list(range(t))); m = eng.load(path13, max_batch=1, max_ctx=256, tp_size=t)
+        s = m.seq_new(); m.prefill(s, p.synth.prompt_tokens(32, m.info.n_vocab)); t13[t] = [int(x) for x in m.decode_greedy(s, 32)]
+        m.close(); eng.close()
+    res["llama2-13b"] = {"tp": n, "tokens_equal_tp1": t13[n] == t13[1], "steps": 32}
+    return res
 
 
 def batch_decode(args, p, eng, path, info, n_seq=32, steps=16):
@@ -421,6 +522,7 @@ def main():
     ap.add_argument("--ctx", type=int, default=512)
     ap.add_argument("--no-batch", action="store_true", help="skip the 32-sequence decode measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-tp", action="store_true", help="skip the tensor-parallel section (llama2-70B over the job's GPUs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -8,7 +8,7 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompil
        --fmad=true -Xptxas -v -ccbin /usr/bin/g++)
 mkdir -p ../build
 objs=()
-for f in dequant.cu gemv.cu attn.cu mega.cu batch.cu gemm.cu gemm_tc.cu step.cu engine.cu engine_batch.cu tp.cu api.cu noalloc.cu gguf.cpp; do
+for f in dequant.cu gemv.cu attn.cu mega.cu batch.cu gemm.cu gemm_tc.cu step.cu engine.cu engine_batch.cu tp.cu api.cu noalloc.cu gguf.cpp tokenizer.cpp tokenizer_api.cpp store.cpp; do
   o=../build/${f%.*}.o
   if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ -n "$(find . ../../include -newer "$o" \( -name '*.h' -o -name '*.cuh' \) -print -quit)" ]; then
     echo "nvcc $f" >&2

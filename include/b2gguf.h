@@ -176,6 +176,41 @@ int b2_debug_read(b2_model* m, int seq, int what, float* out, int n);
 /* Copy cached K and V rows [0, n_tok) of one layer to the host as f16 [n_tok][n_head_kv*head_dim]. */
 int b2_kv_read(b2_model* m, int seq, int layer, uint16_t* k_out, uint16_t* v_out, int n_tok);
 
+/* ---- model store and tokenizer (host only, no GPU needed) ----------------------------------------------
+ * What sits either side of the decode path inside the pod the operator builds: the read-only volume at
+ * /root/.ollama that `ollama pull` filled (reference pkg/model/pod.go:34-40 mount, :68-83 puller,
+ * pkg/model/image_store.go:172-181 store), and the tokenizer every GGUF blob carries in its metadata. */
+typedef struct b2_store_entry {
+    char name[256];             /* canonical [namespace/]model:tag */
+    char model_path[1024];      /* blob of the application/vnd.ollama.image.model layer: the GGUF file */
+    char template_path[1024];   /* prompt template layer ("" if the manifest has none) */
+    char system_path[1024];     /* system prompt layer */
+    char params_path[1024];     /* JSON parameters layer (stop strings, temperature, ...) */
+    char digest[80];            /* sha256:<hex> of the model layer */
+    uint64_t model_size;
+    int64_t modified_unix;
+} b2_store_entry;
+/* models: the store root (a directory with manifests/ and blobs/, or an OLLAMA home whose models/ child has them);
+ * NULL: $OLLAMA_MODELS, $HOME/.ollama/models, /root/.ollama/models.  name: [registry/][namespace/]model[:tag]. */
+int b2_store_resolve(const char* models, const char* name, b2_store_entry* out);
+/* One line per pulled model, "name\tbytes\tdigest\tmtime\n"; returns the bytes the full listing needs. */
+int b2_store_list(const char* models, char* buf, int cap);
+
+typedef struct b2_tokenizer b2_tokenizer;
+typedef struct b2_tokenizer_info {
+    int32_t kind;               /* 1 = SentencePiece-style "llama", 2 = byte-level BPE "gpt2" */
+    int32_t n_vocab, bos, eos, add_bos;
+} b2_tokenizer_info;
+int b2_tokenizer_load(const char* gguf_path, b2_tokenizer** out);
+void b2_tokenizer_free(b2_tokenizer* t);
+int b2_tokenizer_get_info(const b2_tokenizer* t, b2_tokenizer_info* out);
+/* Returns the token count; if it exceeds cap nothing is written (call again with room).  add_bos < 0: the file's
+ * tokenizer.ggml.add_bos_token default.  parse_special: control tokens spelled out in the text become their ids. */
+int b2_tokenize(const b2_tokenizer* t, const char* text, int add_bos, int parse_special, int32_t* out, int cap);
+/* Returns the byte count (terminator not included); beyond cap - 1 nothing is written. */
+int b2_detokenize(const b2_tokenizer* t, const int32_t* toks, int n, int render_special, char* out, int cap);
+int b2_token_piece(const b2_tokenizer* t, int32_t tok, int render_special, char* out, int cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,7 +27,9 @@ static __device__ __forceinline__ void cluster_exchange(uint64_t* xb, uint32_t& 
         asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
     }
     uint32_t ok = 0;
+    SpinGuard guard;
     while (!ok) {
+        guard.tick();
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
             "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"

@@ -56,6 +56,24 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }
 
+// Spin guard: a wait on another CTA, another GPU or an asynchronous copy must not hang the device if that party died
+// (a lost peer, a faulted copy).  `spin_guard(n)` is called once per polling iteration with a running counter; every
+// 4096 iterations it reads the global timer and traps once the wait has lasted longer than B2_SPIN_TIMEOUT_NS, which
+// the host then reports as B2_ERR_CUDA (the context is gone, as after any device-side fault).
+constexpr unsigned long long B2_SPIN_TIMEOUT_NS = 4000000000ull;
+struct SpinGuard {
+    unsigned n = 0;
+    unsigned long long t0 = 0;
+    __device__ __forceinline__ void tick() {
+        if ((++n & 4095u) == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > B2_SPIN_TIMEOUT_NS) __trap();
+        }
+    }
+};
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
@@ -85,8 +103,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    while (!mbar_try_wait(bar, parity)) {
-    }
+    if (mbar_try_wait(bar, parity)) return;
+    SpinGuard guard;
+    while (!mbar_try_wait(bar, parity)) guard.tick();
 }
 
 // L2 policy for data that is streamed exactly once per decode step (the weights)

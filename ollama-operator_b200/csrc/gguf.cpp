@@ -66,6 +66,8 @@ bool read_value(Cursor& c, uint32_t t, GgufValue& v, int depth = 0) {
         const uint32_t et = c.get<uint32_t>();
         const uint64_t n = c.get<uint64_t>();
         v.arr_len = n;
+        v.arr_type = (int)et;
+        v.arr_data = c.p;
         if (const size_t es = scalar_size(et)) {
             uint64_t nbytes = 0;
             if (__builtin_mul_overflow(n, (uint64_t)es, &nbytes)) { c.ok = false; return false; }
@@ -173,6 +175,29 @@ bool GgufFile::get_f64(const std::string& key, double* v) const {
     if (t == 6 || t == 12) { *v = it->second.f; return true; }
     if (t == 8 || t == 9) return false;
     *v = (double)(int64_t)it->second.u;
+    return true;
+}
+bool GgufFile::get_str_array(const std::string& key, std::vector<std::string>* v) const {
+    auto it = kv_.find(key);
+    if (it == kv_.end() || it->second.type != 9 || it->second.arr_type != 8) return false;
+    Cursor c{it->second.arr_data, map_ + size_};
+    v->clear();
+    v->reserve((size_t)it->second.arr_len);
+    for (uint64_t i = 0; i < it->second.arr_len && c.ok; i++) v->push_back(c.str());
+    return c.ok;
+}
+bool GgufFile::get_f32_array(const std::string& key, std::vector<float>* v) const {
+    auto it = kv_.find(key);
+    if (it == kv_.end() || it->second.type != 9 || it->second.arr_type != 6) return false;
+    v->resize((size_t)it->second.arr_len);
+    memcpy(v->data(), it->second.arr_data, v->size() * 4);       // bounds were checked when the array was skipped over in open()
+    return true;
+}
+bool GgufFile::get_i32_array(const std::string& key, std::vector<int32_t>* v) const {
+    auto it = kv_.find(key);
+    if (it == kv_.end() || it->second.type != 9 || (it->second.arr_type != 5 && it->second.arr_type != 4)) return false;
+    v->resize((size_t)it->second.arr_len);
+    memcpy(v->data(), it->second.arr_data, v->size() * 4);
     return true;
 }
 bool GgufFile::get_str(const std::string& key, std::string* v) const {

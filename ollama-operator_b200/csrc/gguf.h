@@ -23,7 +23,9 @@ struct GgufValue {
     uint64_t u = 0;              // integers / bool
     double f = 0;                // floats
     std::string s;               // strings
-    uint64_t arr_len = 0;        // arrays: only the length is kept
+    uint64_t arr_len = 0;        // arrays: element count, element type and where the elements sit in the mapping
+    int arr_type = -1;           // (scalar elements: packed; strings: {u64 length, bytes} one after the other)
+    const uint8_t* arr_data = nullptr;
 };
 
 class GgufFile {
@@ -34,6 +36,10 @@ class GgufFile {
     bool get_u64(const std::string& key, uint64_t* v) const;
     bool get_f64(const std::string& key, double* v) const;
     bool get_str(const std::string& key, std::string* v) const;
+    // arrays (tokenizer.ggml.tokens / scores / token_type / merges): copies out of the mapping
+    bool get_str_array(const std::string& key, std::vector<std::string>* v) const;
+    bool get_f32_array(const std::string& key, std::vector<float>* v) const;
+    bool get_i32_array(const std::string& key, std::vector<int32_t>* v) const;
     const std::vector<GgufTensor>& tensors() const { return tensors_; }
     uint32_t version() const { return version_; }
 

@@ -63,8 +63,8 @@ __device__ __forceinline__ void grid_barrier(unsigned* count, unsigned& epoch, i
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(count) : "memory");
         const unsigned target = epoch * gridDim.x;
         // (polling with relaxed loads plus one acquire fence was measured slower: 1.5-2.1 us per barrier against 1.2-1.5)
-        while (ld_acquire_gpu(count) < target) {
-        }
+        SpinGuard guard;           // a CTA that never arrives (a fault elsewhere) becomes a trap, not a hung GPU
+        while (ld_acquire_gpu(count) < target) guard.tick();
     }
     named_bar_sync(1, ntc);
 }
@@ -80,8 +80,10 @@ __device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf,
         }
         const unsigned* f = tp.flags[tp.rank] + tid;
         unsigned v;
+        SpinGuard guard;           // a peer GPU that never publishes this epoch becomes a trap here
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            guard.tick();
         } while ((int)(v - e) < 0);
     }
     named_bar_sync(1, ntc);

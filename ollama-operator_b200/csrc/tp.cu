@@ -49,8 +49,8 @@ __global__ void __launch_bounds__(256) tp_allreduce_residual_kernel(const TpPeer
     }
     if (threadIdx.x < p.n && (int)threadIdx.x != p.rank) {
         const unsigned* f = p.flags[p.rank] + threadIdx.x;
-        while ((int)(ld_acquire_sys(f) - e) < 0) {
-        }
+        SpinGuard guard;           // a peer that never publishes this epoch becomes a trap (B2_ERR_CUDA on the host), not a hung GPU
+        while ((int)(ld_acquire_sys(f) - e) < 0) guard.tick();
     }
     __syncthreads();
     for (int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x); i < n; i += 2 * gridDim.x * blockDim.x) {

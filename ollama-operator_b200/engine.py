@@ -23,6 +23,7 @@ SYMBOLS = [
     "b2_init", "b2_shutdown", "b2_strerror", "b2_model_load", "b2_model_free", "b2_model_get_info",
     "b2_seq_new", "b2_seq_assume", "b2_seq_free", "b2_seq_len", "b2_seq_truncate", "b2_prefill", "b2_decode", "b2_decode_greedy",
     "b2_get_stats", "b2_mega_trace", "b2_profile_step", "b2_dequantize", "b2_dequantize_repacked", "b2_gemv", "b2_gemm", "b2_gemm_tc", "b2_gemv_noalloc", "b2_gemv_bench", "b2_attn_decode", "b2_attn_bench", "b2_kv_read", "b2_debug_read",
+    "b2_store_resolve", "b2_store_list", "b2_tokenizer_load", "b2_tokenizer_free", "b2_tokenizer_get_info", "b2_tokenize", "b2_detokenize", "b2_token_piece",
 ]
 
 

@@ -1,7 +1,7 @@
 #!/bin/bash
 # quick bench: prints tok/s, roofline fraction and the per-kernel step profile for the given env settings
 export B2_MODEL_DIR=/tmp/b2gguf-models
-python bench.py --steps ${STEPS:-64} --warmup 8 --no-cpu --no-batch ${QB_ARGS:-} 2>&1 | python -c "
+python bench.py --steps ${STEPS:-64} --warmup 8 --no-cpu --no-batch --no-tp ${QB_ARGS:-} 2>&1 | python -c "
 import sys,json
 for l in sys.stdin.read().strip().splitlines():
     try: d=json.loads(l)
