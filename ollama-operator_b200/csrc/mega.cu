@@ -404,16 +404,18 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const uint32_t arrive_units = MEGA_EMPTY_BASE / (uint32_t)(PT * Sw);
         long long c_wait = 0, c_work = 0;      // (trace only) cycles warp 0 spends waiting for tiles / computing
         if (working) {
-            // (tile, pair inside the tile, ring slot, slot phase) of this worker's pair slots, advanced without divisions
-            const int dq = NW / PT, dr = NW - dq * PT;
-            int t = worker / PT, i = worker - t * PT;
-            uint32_t slot = ring_slot + (uint32_t)t, phase = ring_phase;
-            while (slot >= (uint32_t)sm.ns) { slot -= sm.ns; phase ^= 1u; }
-            for (int j = worker; j < ntiles * PT; j += NW) {
+            // Every worker walks every tile of the stage (a parity wait must not skip a lap of its barrier), and computes in
+            // the tiles where it owns a pair slot: slot j = t * PT + i belongs to worker j % NW, and PT <= NW, so at most one.
+            int jn = worker;                                   // this worker's next pair slot
+            uint32_t slot = ring_slot, phase = ring_phase;
+            for (int t = 0; t < ntiles; t++) {
+                const int i = jn - t * PT;                     // pair inside tile t, if 0 <= i < PT
+                const bool own = i < PT;
+                const int j = jn;
                 const long long c0 = tr ? clock64() : 0;
                 if (!(sm.debug & 2)) mbar_wait(&full[slot], phase);
                 const long long c1 = tr ? clock64() : 0;
-                if (j < npairs_cta && !(sm.debug & 1)) {
+                if (own && j < npairs_cta && !(sm.debug & 1)) {
                     // two rows at a time: twice the independent dp4a chains, and one transposed f64 butterfly
                     // (lanes 0-15 end up with row r, lanes 16-31 with row r+1) instead of two
                     const uint8_t* pb = ring + slot * sm.stage_bytes;
@@ -440,11 +442,12 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     if ((lane & 15) == 0) ysum[(2 * j + (upper ? 1 : 0)) * Sw + ch] = keep;
                 }
                 __syncwarp();
-                if (lane == 0 && !(sm.debug & 2)) mbar_arrive_units(&empty[slot], arrive_units);       // this warp no longer reads the slot
+                if (own) {
+                    if (lane == 0 && !(sm.debug & 2)) mbar_arrive_units(&empty[slot], arrive_units);   // this warp no longer reads the slot
+                    jn += NW;
+                }
                 if (tr) { const long long c2 = clock64(); c_wait += c1 - c0; c_work += c2 - c1; }
-                i += dr; slot += (uint32_t)dq;
-                if (i >= PT) { i -= PT; slot++; }
-                while (slot >= (uint32_t)sm.ns) { slot -= sm.ns; phase ^= 1u; }
+                if (++slot == (uint32_t)sm.ns) { slot = 0; phase ^= 1u; }
             }
         }
         if (tr) { tr[12] = (unsigned long long)c_wait; tr[13] = (unsigned long long)c_work; }

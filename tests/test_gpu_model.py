@@ -238,3 +238,20 @@ def test_wide_model_long_prompt_through_the_tensor_core_path(pkg, oracle, eng, m
         tok = int(np.argmax(om.eval(tok)))
     assert got == ref
     m.close()
+
+
+def test_13b_width_tiles_smaller_than_a_worker_round(pkg, oracle, eng, model_dir):
+    """llama2-13B's matrix widths (K = 5120 / 13824) make the persistent kernel's weight tiles hold fewer row pairs than
+    there are row workers, so a worker owns a pair only in some tiles.  The greedy tokens must still be the oracle's and
+    those of the per-matrix kernels (a worker that skipped a tile's barrier lap once read a tile before it had landed)."""
+    path = pkg.synth.cached_model("wide13-llama-1l", model_dir, source="blocks")
+    om = oracle.OracleModel(path, faithful=2)
+    toks = pkg.synth.prompt_tokens(24, om.m.n_vocab)
+    want, _ = om.generate(toks, 48)
+    for flags in (0, pkg.engine.LOAD_NO_MEGA):
+        m = eng.load(path, max_batch=1, max_ctx=128, flags=flags)
+        seq = m.seq_new()
+        lg = m.prefill(seq, toks)
+        got = [int(np.argmax(lg))] + [int(t) for t in m.decode_greedy(seq, 47)]
+        assert got == want, (flags, next(i for i in range(48) if got[i] != want[i]))
+        m.close()
