@@ -18,5 +18,6 @@ for f in dequant.cu gemv.cu attn.cu mega.cu batch.cu gemm.cu gemm_tc.cu step.cu 
 done
 "$NVCC" -shared -o "$OUT" "${objs[@]}" -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -lcudart_static -lrt -lpthread -ldl
 echo "built $(readlink -f $OUT)" >&2
-# the HTTP front end (serve): C ABI only
-g++ -O2 -std=c++17 -Wall -pthread -o "$(dirname "$0")/../server/b2-server" "$(dirname "$0")/../../server/b2_server.cpp" -L.. -lb200gguf -Wl,-rpath,'$ORIGIN/../ollama-operator_b200' 2>&1 | head -20 >&2 || true
+# the HTTP front end (`serve`): uses the C ABI only (cwd is csrc/)
+g++ -O2 -std=c++17 -Wall -pthread -o ../../server/b2-server ../../server/b2_server.cpp -L.. -lb200gguf -Wl,-rpath,'$ORIGIN/../ollama-operator_b200'
+echo "built $(readlink -f ../../server/b2-server)" >&2

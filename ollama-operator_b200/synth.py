@@ -170,6 +170,15 @@ def write_gguf(path: str, cfg: ModelConfig, seed: int = 0x5EED, source: str = "g
         w.add_layer_norm_eps(cfg.norm_eps)
     w.add_vocab_size(V)
     w.add_file_type({"q4_0": 2, "q8_0": 7, "q4_k_m": 15}[cfg.ftype])
+    if V >= 300:
+        # A SentencePiece-style vocabulary that can spell any text: <unk> <s> </s>, the 256 byte-fallback pieces, then
+        # filler word pieces (so that a server can be driven with text against a random-init model).
+        toks = ["<unk>", "<s>", "</s>"] + [f"<0x{b:02X}>" for b in range(256)] + [f"\u2581w{i}" for i in range(V - 259)]
+        w.add_tokenizer_model("llama")
+        w.add_token_list(toks)
+        w.add_token_scores([0.0] * 259 + [-float(i) for i in range(V - 259)])
+        w.add_token_types([2, 3, 3] + [6] * 256 + [1] * (V - 259))
+        w.add_bos_token_id(1); w.add_eos_token_id(2); w.add_unk_token_id(0); w.add_add_bos_token(True)
     types = tensor_types(cfg)
 
     def quant(name: str, rows: int, k: int, std: float):

@@ -84,6 +84,35 @@ static std::string read_text(const char* path) {
     return ss.str();
 }
 
+// Byte-fallback tokens can split a UTF-8 character over several tokens (and a random-init model emits arbitrary bytes):
+// take the longest prefix of `pending` that is complete, valid UTF-8, replacing invalid bytes with U+FFFD; an incomplete
+// sequence at the end stays pending unless `flush`.
+static std::string take_valid_utf8(std::string& pending, bool flush) {
+    std::string out;
+    size_t i = 0;
+    const size_t n = pending.size();
+    while (i < n) {
+        const unsigned char c = (unsigned char)pending[i];
+        const int len = c < 0x80 ? 1 : (c >> 5) == 6 && c >= 0xC2 ? 2 : (c >> 4) == 14 ? 3 : (c >> 3) == 30 && c <= 0xF4 ? 4 : 0;
+        if (len == 0) { out += "\xEF\xBF\xBD"; i++; continue; }
+        if (i + (size_t)len > n) {
+            bool plausible = true;
+            for (size_t k = i + 1; k < n; k++) plausible &= ((unsigned char)pending[k] & 0xC0) == 0x80;
+            if (plausible && !flush) break;                  // wait for the rest of the character
+            out += "\xEF\xBF\xBD"; i++; continue;
+        }
+        bool ok = true;
+        for (int k = 1; k < len; k++) ok &= ((unsigned char)pending[i + k] & 0xC0) == 0x80;
+        if (ok && len == 3) { const unsigned cp = ((c & 0x0F) << 12) | (((unsigned char)pending[i + 1] & 0x3F) << 6); ok = cp >= 0x800 && (cp < 0xD800 || cp > 0xDFFF); }
+        if (ok && len == 4) { const unsigned cp = ((c & 0x07) << 18) | (((unsigned char)pending[i + 1] & 0x3F) << 12); ok = cp >= 0x10000 && cp <= 0x10FFFF; }
+        if (!ok) { out += "\xEF\xBF\xBD"; i++; continue; }
+        out.append(pending, i, (size_t)len);
+        i += (size_t)len;
+    }
+    pending.erase(0, i);
+    return out;
+}
+
 // ---- one generation request, shared between its connection thread and the engine thread -------------------------
 struct Options {
     int num_predict = 128;
@@ -136,7 +165,7 @@ class Engine {
     double last_load_s() const { return last_load_s_; }
 
   private:
-    struct Running { std::shared_ptr<Request> r; int seq; int32_t last; int n_gen; std::mt19937 rng; std::string tail; Clock::time_point t_eval; };
+    struct Running { std::shared_ptr<Request> r; int seq; int32_t last; int n_gen; std::mt19937 rng; std::string tail; Clock::time_point t_eval; std::string utf8; };
 
     void fail(const std::shared_ptr<Request>& r, const std::string& e) {
         std::lock_guard<std::mutex> l(r->mu);
@@ -154,13 +183,15 @@ class Engine {
         unload();
         load_name_ = name;
         if (b2_store_resolve(store_.c_str(), name.c_str(), &entry_) != B2_OK) { load_err_ = std::string("model '") + name + "' not found: " + b2_strerror(); return; }
+        const int tp = std::max(1, std::min(8, getenv("B2_TP_SIZE") ? atoi(getenv("B2_TP_SIZE")) : 1));       // GPUs of this replica (spec.b200.tensorParallel)
         if (!ctx_) {
-            const int dev = 0;
-            if (b2_init(1, &dev, &ctx_) != B2_OK) { load_err_ = b2_strerror(); return; }
+            int devs[8];
+            for (int i = 0; i < tp; i++) devs[i] = i;
+            if (b2_init(tp, devs, &ctx_) != B2_OK) { load_err_ = b2_strerror(); return; }
         }
         b2_load_opts o;
         memset(&o, 0, sizeof o);
-        o.max_batch = max_batch_; o.max_ctx = max_ctx_; o.tp_size = 1;
+        o.max_batch = max_batch_; o.max_ctx = max_ctx_; o.tp_size = tp;
         if (b2_model_load(ctx_, entry_.model_path, &o, &model_) != B2_OK) { load_err_ = b2_strerror(); model_ = nullptr; return; }
         if (b2_tokenizer_load(entry_.model_path, &tok_) != B2_OK) { load_err_ = b2_strerror(); unload(); return; }
         b2_model_get_info(model_, &info_);
@@ -213,6 +244,8 @@ class Engine {
         }
     flush:
         if (tok == tinfo_.eos) { piece = g.tail; g.tail.clear(); }
+        g.utf8 += piece;
+        piece = take_valid_utf8(g.utf8, stop);
         {
             std::lock_guard<std::mutex> l(r.mu);
             if (tok != tinfo_.eos) r.generated.push_back(tok);
@@ -225,7 +258,9 @@ class Engine {
         Request& r = *g.r;
         b2_seq_free(model_, g.seq);
         std::lock_guard<std::mutex> l(r.mu);
-        if (!g.tail.empty()) r.pieces.push_back(g.tail);
+        g.utf8 += g.tail;
+        const std::string rest = take_valid_utf8(g.utf8, true);
+        if (!rest.empty()) r.pieces.push_back(rest);
         r.eval_s = std::chrono::duration<double>(Clock::now() - g.t_eval).count();
         r.done_reason = reason;
         r.done = true;
