@@ -309,12 +309,13 @@ def run_gpu(args):
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4,
                 "gpu_ms_per_step": e2e_gpu_ms / args.steps},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_source": None if traffic is None else "dram__bytes_read+write of one ncu --set full capture of this kernel (profiles/traffic.json, taken at another context length) + the KV rows this context adds; not measured in this run",
                      "kernel": k_name, "bytes_per_launch": k_bytes, "ms_per_launch": k_ms,
                      "peak_source": peak_src,
                      "step": {"bytes": step_bytes, "achieved": step_gbs, "frac": step_gbs / peak}},
         "profile_step_ms": {k: round(v, 4) for k, v in prof_ms.items() if v > 0},
         "prefill": {"tokens": args.ctx, "ms": prefill_ms, "tok_s": args.ctx / (prefill_ms * 1e-3),
-                    "note": "chunks of 32 tokens per weight pass through the batched W4A8 kernel (bit-identical to token-by-token)"},
+                    "note": "prompt chunks of up to 512 columns per weight pass through the tcgen05 kernel (kind::i8 MMA per 32-weight block, TMEM accumulators, f64 term accumulation: bit-identical to token-by-token)"},
         "setup_s": {"write_gguf": round(gen_s, 1), "load": round(load_s, 1)},
     }
     if world == 1 and not args.no_cpu:
