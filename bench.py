@@ -331,10 +331,13 @@ def run_gpu(args):
             out["tp"] = tp_section(args, p, world)
         except Exception as e:          # the replica headline above stands on its own
             out["tp"] = {"error": f"{type(e).__name__}: {e}"}
+    print(json.dumps(out), flush=True)          # the line is out before any teardown that a faulted context could stall
     if dist:
-        dist.barrier(group=host_group)
-        dist.destroy_process_group()
-    print(json.dumps(out))
+        try:
+            dist.barrier(group=host_group)
+            dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 def tp_run(p, path, tp, ctx, steps, n_batch, peak):

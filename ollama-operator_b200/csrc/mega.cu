@@ -150,7 +150,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     if (warp == NCW) {
         // ===== producer: this CTA's tiles of every GEMV stage, in stage order =====
         if (lane == 0 && !(sm.debug & 2)) {
-            const uint64_t pol = l2_policy_evict_first();
+            const uint64_t pol = (sm.debug & 4) ? l2_policy_evict_last() : (sm.debug & 8) ? l2_policy_evict_normal() : l2_policy_evict_first();
             // cursor over (stage, tile) pairs; two of them walk the same sequence: `f` feeds the
             // shared-memory ring, `p` runs up to sm.pf_bytes further ahead issuing L2 prefetches, so
             // that HBM keeps streaming while the consumers sit in a barrier, a prologue or the

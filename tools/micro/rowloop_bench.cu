@@ -56,15 +56,34 @@ constexpr int NU = 128;                 // units per row (K = 4096)
 constexpr int QS = NU * 16, SS = NU * 2;    // plane strides
 constexpr int RT = 32;                  // rows in the tile
 
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 template <int V>
 __global__ void __launch_bounds__(512, 1) k(const uint8_t* gq, const uint8_t* gs, int iters, int nact, long long* out, double* sink) {
     extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t sbar[2];
+    __shared__ volatile int sdone;
     uint8_t* q = smem; uint8_t* sc = smem + RT * QS;
     for (int i = threadIdx.x; i < RT * QS / 16; i += blockDim.x) reinterpret_cast<uint4*>(q)[i] = reinterpret_cast<const uint4*>(gq)[i];
     for (int i = threadIdx.x; i < RT * SS / 16; i += blockDim.x) reinterpret_cast<uint4*>(sc)[i] = reinterpret_cast<const uint4*>(gs)[i];
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp >= nact) return;
+    if (V == 5) {
+        if (threadIdx.x == 0) { sdone = 0; for (int i = 0; i < 2; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&sbar[i]))); asm volatile("fence.mbarrier_init.release.cluster;"); }
+        __syncthreads();
+        if (warp == 15) {      // streamer: 64 KB bulk copies from global into a scratch region of shared memory, back to back, while the others compute
+            if (lane == 0) {
+                uint8_t* dst = smem + RT * (QS + SS);
+                for (int it = 0; !sdone; it++) {
+                    const int b = it & 1;
+                    if (it >= 2) { uint32_t ok = 0; while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(s32(&sbar[b])), "r"(((it >> 1) - 1) & 1)); }
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(&sbar[b])), "r"(32768));
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s32(dst + b * 32768)), "l"(gq + (size_t)((blockIdx.x * 7 + it) % 1024) * 32768), "r"(32768), "r"(s32(&sbar[b])));
+                }
+            }
+            return;
+        }
+    }
+    if (warp >= nact) { return; }
     asm volatile("bar.sync 1, %0;" :: "r"(nact * 32));
     X x[4]; int unit[4];
 #pragma unroll
@@ -75,11 +94,11 @@ __global__ void __launch_bounds__(512, 1) k(const uint8_t* gq, const uint8_t* gs
     }
     double total = 0;
     const long long t0 = clock64();
-    if (V == 0 || V == 1) {                     // current structure: two rows, butterfly each iteration (V1: f32 accumulation)
+    if (V == 0 || V == 1 || V == 5) {                     // current structure: two rows, butterfly each iteration (V1: f32 accumulation)
         for (int it = 0; it < iters; it++) {
             const int r = (2 * warp + 2 * it) % RT;
             const uint8_t *q0 = q + r * QS, *q1 = q0 + QS, *s0 = sc + r * SS, *s1 = s0 + SS;
-            if (V == 0) {
+            if (V == 0 || V == 5) {
                 double a0 = 0, a1 = 0;
 #pragma unroll
                 for (int j = 0; j < 4; j++) { a0 += (double)unit_dot(x[j], q0, s0, unit[j]); a1 += (double)unit_dot(x[j], q1, s1, unit[j]); }
@@ -127,15 +146,16 @@ __global__ void __launch_bounds__(512, 1) k(const uint8_t* gq, const uint8_t* gs
         }
     }
     const long long t1 = clock64();
+    if (V == 5) { asm volatile("bar.sync 2, %0;" ::"r"(nact * 32)); if (threadIdx.x == 0) sdone = 1; }
     if (lane == 0) out[blockIdx.x * 16 + warp] = t1 - t0;
     if (total == 1.2345) sink[0] = total;
 }
 
 template <int V> void run(const char* name, const uint8_t* gq, const uint8_t* gs, long long* dout, double* sink, int iters) {
-    const int smem = RT * (QS + SS);
+    const int smem = RT * (QS + SS) + (V == 5 ? 65536 : 0);
     CK(cudaFuncSetAttribute(k<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     static long long h[148 * 16];
-    for (int nact : {1, 8, 15}) {
+    for (int nact : {8, 15}) {
         k<V><<<148, 512, smem>>>(gq, gs, iters, nact, dout, sink);
         CK(cudaDeviceSynchronize());
         CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
@@ -151,7 +171,7 @@ int main() {
     for (size_t i = 0; i < nq; i++) hq[i] = (uint8_t)(rand() & 0xFF);
     for (size_t i = 0; i < ns / 2; i++) reinterpret_cast<__half*>(hs)[i] = __float2half(0.01f + (rand() % 100) * 1e-4f);
     uint8_t *gq, *gs; long long* dout; double* sink;
-    CK(cudaMalloc(&gq, nq)); CK(cudaMalloc(&gs, ns)); CK(cudaMalloc(&dout, 148 * 16 * 8)); CK(cudaMalloc(&sink, 8));
+    CK(cudaMalloc(&gq, (size_t)1024 * 32768 + nq)); CK(cudaMalloc(&gs, ns)); CK(cudaMalloc(&dout, 148 * 16 * 8)); CK(cudaMalloc(&sink, 8));
     CK(cudaMemcpy(gq, hq, nq, cudaMemcpyHostToDevice)); CK(cudaMemcpy(gs, hs, ns, cudaMemcpyHostToDevice));
     for (int it : {1, 2, 4, 6, 12}) { printf("-- short runs: %d iterations per warp (cold start after a block barrier)\n", it); run<0>("V0 short", gq, gs, dout, sink, it); run<2>("V2 short", gq, gs, dout, sink, it); }
     const int iters = 400;
@@ -160,5 +180,6 @@ int main() {
     run<2>("V2 deferred butterfly", gq, gs, dout, sink, iters);
     run<3>("V3 four rows", gq, gs, dout, sink, iters);
     run<4>("V4 four rows, tree cvt", gq, gs, dout, sink, iters);
+    run<5>("V5 = V0 + bulk copies into smem", gq, gs, dout, sink, iters);
     return 0;
 }
