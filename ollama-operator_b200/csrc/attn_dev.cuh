@@ -162,6 +162,60 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     // ---- 1. scores of this CTA's slice of the context ---------------------------------------------
     const int per = (n + CL - 1) / CL;
     const int t_begin = min(n, (int)rk * per), t_end = min(n, t_begin + per);
+    if (HD == 128 && GRP == 1) {
+        // Wide K rows (one query head, head_dim 128): four lanes share a position, lane j0 of them loads the 16-byte chunks
+        // j0, j0 + 4, j0 + 8, j0 + 12 of the 256-byte row and thereby owns the eight complete FMA chains L = 8 j0 + e
+        // (chain L runs over dims L, L + 32, L + 64, L + 96, in that order -- ggml's lane structure).  Four 128-bit loads
+        // per lane replace thirty-two 16-bit ones (the 2-byte loads, not their latency, bounded this phase); the chains
+        // are then combined in exactly the order of reduce_lanes32: L^16 and L^8 live in the lanes j0^2 and j0^1, L^4, L^1
+        // and L^2 partly in the thread itself.
+        const int j0 = lane & 3, pg = lane >> 2;
+        const bool b1 = (j0 & 2) != 0, b0 = (j0 & 1) != 0;
+        float qr[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int e = 0; e < 8; e++) qr[i][e] = qs[32 * i + 8 * j0 + e];
+        for (int t0 = t_begin + warp * 8; t0 < t_end; t0 += NWARP * 8) {
+            const int t = min(t0 + pg, t_end - 1);
+            const __half* kr = k_base + rowoff[t] + 8 * j0;
+            uint4 kq[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) kq[i] = *reinterpret_cast<const uint4*>(kr + 32 * i);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; e++) v[e] = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const __half2* h2 = reinterpret_cast<const __half2*>(&kq[i]);
+#pragma unroll
+                for (int e2 = 0; e2 < 4; e2++) {
+                    const float2 f = __half22float2(h2[e2]);
+                    v[2 * e2] = fmaf(f.x, qr[i][2 * e2], v[2 * e2]);
+                    v[2 * e2 + 1] = fmaf(f.y, qr[i][2 * e2 + 1], v[2 * e2 + 1]);
+                }
+            }
+            float k4[4], k2[2];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {                 // L ^ 16: lane ^ 2; this lane keeps e in [4 b1, 4 b1 + 4)
+                const float keep = b1 ? v[4 + i] : v[i], send = b1 ? v[i] : v[4 + i];
+                k4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; i++) {                 // L ^ 8: lane ^ 1; keeps e = 4 b1 + 2 b0 + i
+                const float keep = b0 ? k4[2 + i] : k4[i], send = b0 ? k4[i] : k4[2 + i];
+                k2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; i++) k2[i] = k2[i] + __shfl_xor_sync(0xffffffffu, k2[i], 2);      // L ^ 4
+            float r = k2[0] + k2[1];                                                                   // L ^ 1
+            r = r + __shfl_xor_sync(0xffffffffu, r, 1);                                                // L ^ 2
+            if (t0 + pg < t_end) {
+                r = __fmul_rn(r, scale);
+                for (int peer = j0; peer < CL; peer += 4) dsmem_st_f32(dsmem_addr(sc + t, (uint32_t)peer), r);
+            }
+        }
+    } else
     {
         float qreg[GRP][NI];
 #pragma unroll
@@ -290,7 +344,7 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
             for (int g = 0; g < GRP; g++)
 #pragma unroll
                 for (int j = 0; j < 8; j++) acc[g][j] = 0.f;
-            constexpr int UV = GRP >= 4 ? 4 : 8;        // V rows in flight per lane
+            constexpr int UV = GRP >= 4 ? 4 : GRP == 1 ? 16 : 8;        // V rows in flight per lane
             for (int tb = c; tb < n; tb += 32 * UV) {
                 uint4 vv[UV];
 #pragma unroll

@@ -381,7 +381,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             mbar_wait(&dbar[db ^ 1], (uint32_t)((st + 1 - s_begin) >> 1) & 1u);      // issued a stage ago (or at kernel start)
             next_is_attn = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->kind == 1;
         }
-        if (next_is_attn) {
+        if (next_is_attn && !(sm.debug & 16)) {
             const AttnArgs& na = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->at;
             const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
             for (int kvh = my_cluster; kvh < na.n_head_kv; kvh += n_clusters) attn_prefetch<GRP, HD, ntc>(na, cluster_size, kvh, tid, pos_now, s_pt);
