@@ -60,22 +60,32 @@ template <int GRP, int HD, int NT>
 static __device__ __forceinline__ void attn_prefetch(const AttnArgs& a, int cluster, int kvh, int tid, int pos_value, const int* page_table) {
     const uint32_t rk = cluster_ctarank();
     const int n = pos_value + 1;
-    const int per = (n + cluster - 1) / cluster;
+    // cluster is 1, 2 or 4 and pages are a power of two: shifts, no integer divisions on the path of the stage that issues this
+    const int cshift = __ffs(cluster) - 1, pshift = __ffs(a.page_tokens) - 1, pmask = a.page_tokens - 1;
+    const int per = (n + cluster - 1) >> cshift;
     const int t_begin = min(n, (int)rk * per), t_end = min(n, t_begin + per);
     constexpr int KLINES = (HD * 2 + 127) / 128;                       // 128-byte lines per K row
     for (int i = tid; i < (t_end - t_begin) * KLINES; i += NT) {
         const int t = t_begin + i / KLINES;
-        const int page = page_table[t / a.page_tokens];
-        const __half* p = a.k_base + ((size_t)page * a.page_tokens + t % a.page_tokens) * a.kv_dim + (size_t)kvh * HD + (i % KLINES) * 64;
+        const int page = page_table[t >> pshift];
+        const __half* p = a.k_base + (((size_t)page << pshift) + (t & pmask)) * a.kv_dim + (size_t)kvh * HD + (i % KLINES) * 64;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     }
-    const int dpc = HD / cluster;                                      // this CTA's output dims
+    const int dpc = HD >> cshift;                                      // this CTA's output dims
     const int vlines = (dpc * 2 + 127) / 128;
-    for (int i = tid; i < n * vlines; i += NT) {
-        const int t = i / vlines;
-        const int page = page_table[t / a.page_tokens];
-        const __half* p = a.v_base + ((size_t)page * a.page_tokens + t % a.page_tokens) * a.kv_dim + (size_t)kvh * HD + (int)rk * dpc + (i % vlines) * 64;
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    if (vlines == 1) {
+        for (int t = tid; t < n; t += NT) {
+            const int page = page_table[t >> pshift];
+            const __half* p = a.v_base + (((size_t)page << pshift) + (t & pmask)) * a.kv_dim + (size_t)kvh * HD + (int)rk * dpc;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+        }
+    } else {
+        for (int i = tid; i < n * vlines; i += NT) {
+            const int t = i / vlines;
+            const int page = page_table[t >> pshift];
+            const __half* p = a.v_base + (((size_t)page << pshift) + (t & pmask)) * a.kv_dim + (size_t)kvh * HD + (int)rk * dpc + (i % vlines) * 64;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+        }
     }
 }
 

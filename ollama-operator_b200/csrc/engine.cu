@@ -658,7 +658,12 @@ int Model::setup_mega(Slot& s) {
         cudaGetLastError();          // does not fit: keep the per-matrix path, and leave no stale CUDA error behind
         return B2_OK;
     }
-    for (auto& x : st) x.att_max_local = L.att_max_local;
+    for (auto& x : st) {
+        x.att_max_local = L.att_max_local;
+        mega_finish_stage(x, L.grid);
+        // (x * inv) >> 16 is exact only for small x: the per-CTA pair count must stay far below 2^16 / PT
+        if (x.kind == 0 && x.pairs_base + 1 + x.PT >= 4096) return B2_OK;
+    }
     B2_CUDA(cudaMalloc(&s.d_stages, st.size() * sizeof(MegaStage)));
     B2_CUDA(cudaMemcpy(s.d_stages, st.data(), st.size() * sizeof(MegaStage), cudaMemcpyHostToDevice));
     L.stages = s.d_stages; L.s_begin = 0; L.s_end = (int)st.size(); L.grid_count = s.d_grid_count;

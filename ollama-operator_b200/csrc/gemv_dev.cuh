@@ -20,13 +20,14 @@ __device__ __forceinline__ float h2f(const __half h) { return __half2float(h); }
 struct ProStats { float mean, scale; };
 
 // Sum over the consumer threads of a double, same value returned to every thread.
-static __device__ double consumers_sum(double v, double* scratch, int tid, int ntc) {
+// `reuse_barrier` = false: the caller guarantees a consumer barrier between this call and the next use of `scratch`
+static __device__ double consumers_sum(double v, double* scratch, int tid, int ntc, bool reuse_barrier = true) {
     v = warp_sum_d(v);
     if ((tid & 31) == 0) scratch[tid >> 5] = v;
     named_bar_sync(1, ntc);
     double s = 0;
     for (int w = 0; w < ntc / 32; w++) s += scratch[w];
-    named_bar_sync(1, ntc);
+    if (reuse_barrier) named_bar_sync(1, ntc);
     return s;
 }
 

@@ -103,6 +103,10 @@ struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident i
     int RPG = 2, RT = 2;          // rows per group per tile, rows per tile (= 2 * PT)
     int PT = 1;                   // row pairs per tile (one ring slot); PT * S owner warps release a slot
     int nunits = 0, nbeff = 4;    // units per row, units per lane actually used
+    // filled in by mega_finish_stage once the grid is known, so that the kernel divides nothing per stage:
+    int pairs_base = 0, pairs_rem = 0;   // row pairs per CTA; the first pairs_rem CTAs take one more
+    int inv_S = 65536, inv_PT = 65536;   // ceil(2^16 / S), ceil(2^16 / PT): x / S == (x * inv_S) >> 16 for the small x used
+    uint32_t arrive_units = 0;           // MEGA_EMPTY_BASE / (PT * S)
     AttnArgs at;
     int att_max_local = 0;
     int tp_buf = 0, tp_n = 0;     // kind 2: which partial-sum buffer, vector length
@@ -126,6 +130,7 @@ struct MegaLaunch {
     TpPeers tp;                          // peers of the exchange stages (tp.n == 1: none)
 };
 bool mega_supported(int type, int grp, int head_dim);
+void mega_finish_stage(MegaStage& st, int grid);
 int mega_plan_stage(MegaStage& st, int ncw, int nb_max);
 double mega_plan_cost(const QMat& W, int nb_max);      // estimated consumer cost of a matrix with at most nb_max units per lane
 int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);

@@ -122,7 +122,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int ntc = NCW * 32;
     constexpr int NP = TYPE == T_Q4_0 || TYPE == T_Q8_0 ? 2 : TYPE == T_Q4_K ? 3 : 4;      // T_KQ: up to 4, the matrix says how many
-    const int cluster_size = (int)cluster_nctarank();
+    const int cluster_size = (int)cluster_nctarank();                            // 1, 2 or 4
+    const int n_clusters = gridDim.x >> (__ffs(cluster_size) - 1), my_cluster = blockIdx.x >> (__ffs(cluster_size) - 1);
     // position and page table of this step: fetched once, used by every layer's KV append and attention
     __shared__ int s_pos;
     __shared__ int s_pt[MEGA_MAX_PAGES];
@@ -165,10 +166,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 for (; c.st < s_end; c.st++) {
                     const MegaStage& S = stages[c.st];
                     if (S.kind != 0) continue;
-                    const uint32_t pairs = (uint32_t)(S.g.W.rows >> 1);
-                    const uint32_t row0 = 2 * (blockIdx.x * pairs / gridDim.x), r_end = 2 * ((blockIdx.x + 1) * pairs / gridDim.x);
-                    if (row0 >= r_end) continue;
-                    c.rows_left = (int)(r_end - row0);
+                    // row pairs of this CTA: pairs_base each, the first pairs_rem CTAs one more (the consumers use the same split)
+                    const uint32_t row0 = 2u * (blockIdx.x * (uint32_t)S.pairs_base + min(blockIdx.x, (uint32_t)S.pairs_rem));
+                    c.rows_left = 2 * (S.pairs_base + (blockIdx.x < (uint32_t)S.pairs_rem ? 1 : 0));
+                    if (c.rows_left <= 0) continue;
                     c.RT = S.RT;
 #pragma unroll
                     for (int pl = 0; pl < NP; pl++) {
@@ -264,7 +265,6 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             AttnCfg ac;
             ac.cluster = cluster_size;
             ac.max_local = S.att_max_local;
-            const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
             if (GRP > 1 && 2 * a.n_head_kv <= n_clusters) {
                 // few KV heads (GQA under tensor parallelism): one query head per cluster instead of one group
                 for (int h = my_cluster; h < a.n_head; h += n_clusters)
@@ -310,11 +310,12 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 double ss = 0;
 #pragma unroll
                 for (int c = 0; c < MAXC; c++) {
+                    if (c * ntc >= nchunks) break;          // (the chunks past the vector are zeros: skipping them changes nothing)
                     ss += (double)__fmul_rn(xv[c].x, xv[c].x); ss += (double)__fmul_rn(xv[c].y, xv[c].y);
                     ss += (double)__fmul_rn(xv[c].z, xv[c].z); ss += (double)__fmul_rn(xv[c].w, xv[c].w);
                 }
                 if (tr) tr[5] = (unsigned long long)clock64();      // (x arrived, squares summed per thread)
-                ss = consumers_sum(ss, dscratch, tid, ntc);
+                ss = consumers_sum(ss, dscratch, tid, ntc, false);      // (the barrier after the quantisation separates it from the next use)
                 const float mean = (float)(ss / (double)K);
                 scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, a.eps)));
             }
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         named_bar_sync(1, ntc);
         if (tr) tr[8] = (unsigned long long)clock64();              // (block barrier)
 
-        const int worker = warp / Sw, ch = warp % Sw;
+        const int worker = (warp * S.inv_S) >> 16, ch = warp - worker * Sw;      // warp / Sw, warp % Sw (reciprocal from the host)
         const bool working = worker < NW;
         XRegs<TYPE> xr[NB];
         int unit[NB];
@@ -383,13 +384,12 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         }
         if (next_is_attn && !(sm.debug & 16)) {
             const AttnArgs& na = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->at;
-            const int n_clusters = gridDim.x / cluster_size, my_cluster = blockIdx.x / cluster_size;
             for (int kvh = my_cluster; kvh < na.n_head_kv; kvh += n_clusters) attn_prefetch<GRP, HD, ntc>(na, cluster_size, kvh, tid, pos_now, s_pt);
         }
 
         // rows [r_begin, r_end) of this CTA: whole pairs, split evenly (32-bit: pairs * grid < 2^31 for every supported matrix)
-        const uint32_t pairs = (uint32_t)(a.W.rows >> 1);
-        const int r_begin = (int)(2 * (blockIdx.x * pairs / gridDim.x)), r_end = (int)(2 * ((blockIdx.x + 1) * pairs / gridDim.x));
+        const int r_begin = (int)(2u * (blockIdx.x * (uint32_t)S.pairs_base + min(blockIdx.x, (uint32_t)S.pairs_rem)));
+        const int r_end = r_begin + 2 * (S.pairs_base + (blockIdx.x < (uint32_t)S.pairs_rem ? 1 : 0));
         // the stage descriptor lives in global memory and the waits below are compiler barriers: keep what
         // the row loop needs in registers
         uint32_t wstride[NP];
@@ -400,9 +400,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         // producer refill as soon as PT owners are done instead of waiting for all fifteen warps.
         const int PT = S.PT;
         const int npairs_cta = (r_end - r_begin) >> 1;
-        const int ntiles = (npairs_cta + PT - 1) / PT;
-        const uint32_t arrive_units = MEGA_EMPTY_BASE / (uint32_t)(PT * Sw);
+        const int ntiles = ((npairs_cta + PT - 1) * S.inv_PT) >> 16;             // ceil(npairs_cta / PT)
+        const uint32_t arrive_units = S.arrive_units;                            // MEGA_EMPTY_BASE / (PT * Sw)
         long long c_wait = 0, c_work = 0;      // (trace only) cycles warp 0 spends waiting for tiles / computing
+        if (tr) tr[14] = (unsigned long long)clock64();           // (stage set-up done, row loop starts)
         if (working) {
             // Every worker walks every tile of the stage (a parity wait must not skip a lap of its barrier), and computes in
             // the tiles where it owns a pair slot: slot j = t * PT + i belongs to worker j % NW, and PT <= NW, so at most one.
@@ -457,6 +458,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         // ---- deferred epilogue: all row sums of this CTA are in shared memory; one thread per row pair,
         //      so the long-latency parts (f64 exp of SiLU, RoPE table, KV page lookup) are paid once ----
         named_bar_sync(1, ntc);
+        if (tr) tr[15] = (unsigned long long)clock64();           // (every warp's row loop done)
         {
             unsigned long long best = 0ull;
             const int npairs = (int)((r_end - r_begin) >> 1);
@@ -528,6 +530,17 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
     st.RT = 2 * pt;
     st.P = 1; st.RPG = 0;
     return B2_OK;
+}
+
+// Per-stage constants that depend on the grid (known after mega_configure): the kernel reads them instead of dividing.
+void mega_finish_stage(MegaStage& st, int grid) {
+    if (st.kind != 0) return;
+    const int pairs = (int)(st.g.W.rows >> 1);
+    st.pairs_base = pairs / grid;
+    st.pairs_rem = pairs % grid;
+    st.inv_S = (65536 + st.S - 1) / st.S;
+    st.inv_PT = (65536 + st.PT - 1) / st.PT;
+    st.arrive_units = MEGA_EMPTY_BASE / (uint32_t)(st.PT * st.S);
 }
 
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
@@ -621,6 +634,7 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
     L.off_xs = (uint32_t)off; off += (size_t)(kq ? k_max / 16 : k_max / 32) * 4; off = (off + 15) / 16 * 16;
     L.off_att = (uint32_t)off;
     L.att_max_local = (max_ctx + 3) / 4 * 4;
+    if (L.cluster != 1 && L.cluster != 2 && L.cluster != 4) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: cluster size %d (1, 2 or 4)", L.cluster);
     if (L.head_dim % (8 * L.cluster)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: head_dim %d does not split over a cluster of %d", L.head_dim, L.cluster);
     off += attndev::attn_smem_bytes(L.grp, L.head_dim, L.att_max_local, L.cluster, MEGA_NCW * 32);
     off = (off + 127) / 128 * 128;

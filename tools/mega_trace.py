@@ -41,6 +41,7 @@ for k, nm in ((0, "qkv"), (3, "up"), (4, "down")):
 for k, nm in ((0, "qkv"), (2, "wo"), (3, "up"), (4, "down")):
     g = tr[:, 15 * 5 + k, :]
     loop = (g[:, 11] - g[:, 9]) / 1.9e3
+    print(f"body {nm}: set-up before the row loop {((g[:, 14] - g[:, 9]) / 1.9e3).mean():.2f} us, loop {((g[:, 11] - g[:, 14]) / 1.9e3).mean():.2f}, wait for the other warps {((g[:, 15] - g[:, 11]) / 1.9e3).mean():.2f}, epilogue {((g[:, 3] - g[:, 2]) / 1e3 - (g[:, 15] - g[:, 9]) / 1.9e3).mean():.2f}")
     tail = (g[:, 3] - g[:, 2]) / 1e3 - loop
     print(f"body {nm}: warp 0 waits for tiles {(g[:, 12] / 1.9e3).mean():.2f} us, computes {(g[:, 13] / 1.9e3).mean():.2f} us")
     print(f"body {nm}: warp 0 row loop mean {loop.mean():.2f} max {loop.max():.2f} us; rest of the body (wait for the other warps + epilogue) mean {tail.mean():.2f} max {tail.max():.2f} us")
