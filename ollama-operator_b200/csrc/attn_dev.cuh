@@ -14,6 +14,7 @@ constexpr int MAX_CLUSTER = 8;
 struct AttnCfg {
     int cluster;        // CTAs per (slot, kv head)
     int max_local;      // capacity of the score buffer: ALL positions of the sequence (every CTA holds them)
+    bool ll_out = false;    // also write the hand-over copy a.out_ll and re-poison a.out_ll_poison (persistent kernel, see GemvArgs::x_ll)
 };
 
 // One all-to-all step between the CTAs of a cluster without involving threads outside the NT
@@ -397,7 +398,12 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
                 const float a2 = v[(c + 4) * dpc] + v[(c + 20) * dpc], a3 = v[(c + 12) * dpc] + v[(c + 28) * dpc];
                 s4[c] = (a0 + a1) + (a2 + a3);
             }
-            a.out[((size_t)kvh * GRP + g) * HD + dbase + d] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            const float r = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            a.out[((size_t)kvh * GRP + g) * HD + dbase + d] = r;
+            if (c.ll_out) {
+                ll_store(a.out_ll + ((size_t)kvh * GRP + g) * HD + dbase + d, r);
+                ll_store(a.out_ll_poison + ((size_t)kvh * GRP + g) * HD + dbase + d, __uint_as_float(LL_POISON));
+            }
         }
     } else
     {
@@ -435,7 +441,13 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
 #pragma unroll
         for (int g = 0; g < GRP; g++) {
             const float r = reduce8_lanes32(acc[g], lane);
-            if ((lane & 3) == 0) a.out[((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane)] = r;
+            if ((lane & 3) == 0) {
+                a.out[((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane)] = r;
+                if (c.ll_out) {
+                    ll_store(a.out_ll + ((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane), r);
+                    ll_store(a.out_ll_poison + ((size_t)kvh * GRP + g) * HD + dbase + d0 + reduce8_index(lane), __uint_as_float(LL_POISON));
+                }
+            }
         }
     }
     }

@@ -61,6 +61,23 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 // 4096 iterations it reads the global timer and traps once the wait has lasted longer than B2_SPIN_TIMEOUT_NS, which
 // the host then reports as B2_ERR_CUDA (the context is gone, as after any device-side fault).
 constexpr unsigned long long B2_SPIN_TIMEOUT_NS = 4000000000ull;
+// ---- hand-over buffers ("flag in data"): a word is LL_POISON until its value has been stored ----
+constexpr uint32_t LL_POISON = 0xFFFFFFFFu;        // a NaN with a full payload: FADD/FMUL/FFMA only ever produce 0x7FFFFFFF
+__device__ __forceinline__ void ll_store(float* p, float v) {
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void ll_store2(float* p, float v0, float v1) {                     // p 8-byte aligned
+    asm volatile("st.relaxed.gpu.global.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(v0), "f"(v1) : "memory");
+}
+__device__ __forceinline__ float4 ll_load4(const float* p) {                                  // p 16-byte aligned; every word is read once, whole
+    float4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool ll_ready(const float4& v) {
+    return __float_as_uint(v.x) != LL_POISON && __float_as_uint(v.y) != LL_POISON && __float_as_uint(v.z) != LL_POISON && __float_as_uint(v.w) != LL_POISON;
+}
+
 struct SpinGuard {
     unsigned n = 0;
     unsigned long long t0 = 0;

@@ -379,7 +379,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
                  o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
                  o_pos = carve(4), o_key = carve(8), o_gc = carve(4), o_out = carve((size_t)out_cap * 4),
-                 o_forced = carve((size_t)max_ctx * 4);
+                 o_forced = carve((size_t)max_ctx * 4), o_xll = carve((size_t)E * 8), o_attll = carve((size_t)nq * 8);
     const size_t slot_bytes = align_up(off, 256);
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
     B2_CUDA(cudaMemset(slot_mem, 0, slot_bytes * max_batch));
@@ -392,6 +392,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
         s.att = (float*)(b + o_att); s.att2 = (float*)(b + o_att2); s.h = (float*)(b + o_h); s.logits = (float*)(b + o_logits);
         s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
         s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced); s.d_grid_count = (unsigned*)(b + o_gc);
+        s.x_ll[0] = (float*)(b + o_xll); s.x_ll[1] = s.x_ll[0] + E; s.att_ll[0] = (float*)(b + o_attll); s.att_ll[1] = s.att_ll[0] + nq;
     }
     // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (ggml_rope_cache_init with
     // ext_factor 0: theta_base starts at pos and is multiplied by freq_base^(-2/n_rot) once per pair; the angle is
@@ -653,6 +654,29 @@ int Model::setup_mega(Slot& s) {
             st.push_back(x);
         }
     }
+    // Stage hand-overs through tagged values instead of a grid barrier (mega.cu, `ll_in`): where a GEMV stage of the fast
+    // prologue path reads exactly the vector the stage before it wrote (attention -> wo, wo -> up, down -> next qkv).
+    if (tp_size <= 1 && !getenv("B2_MEGA_NO_LL")) {
+        int wx = 0, wa = 0;          // writes of x / att so far in the step: write w uses buffer w % 2 and re-poisons the other
+        for (size_t i = 1; i < st.size(); i++) {
+            MegaStage& c = st[i];
+            MegaStage& p = st[i - 1];
+            if (c.kind != 0) continue;
+            const GemvArgs& g = c.g;
+            const bool fast = (g.W.type == T_Q4_0 || g.W.type == T_Q8_0) && (g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 128 == 0 &&
+                              g.W.k / 4 <= (int64_t)6 * MEGA_NCW * 32;          // the kernel's fast prologue path (mega.cu)
+            if (!fast) continue;
+            if (p.kind == 1 && p.at.out == g.x && g.W.k == (int64_t)hp.n_head * hp.head_dim) {
+                p.at.out_ll = s.att_ll[wa & 1]; p.at.out_ll_poison = s.att_ll[(wa + 1) & 1]; c.g.x_ll = s.att_ll[wa & 1]; c.ll_in = 1; wa++;
+            } else if (p.kind == 0 && p.g.epi == EPI_RESIDUAL && p.g.y == g.x && p.g.epi_row0 == 0 && p.g.W.rows == g.W.k && g.W.k == hp.n_embd) {
+                p.g.y_ll = s.x_ll[wx & 1]; p.g.y_ll_poison = s.x_ll[(wx + 1) & 1]; c.g.x_ll = s.x_ll[wx & 1]; c.ll_in = 1; wx++;
+            }
+        }
+        if (wx) { L.ll_init[0] = s.x_ll[0]; L.ll_init_n[0] = hp.n_embd; }
+        if (wa) { L.ll_init[1] = s.att_ll[0]; L.ll_init_n[1] = hp.n_head * hp.head_dim; }
+    }
+    for (size_t i = 0; i + 1 < st.size(); i++)
+        if (st[i].kind == 0 && st[i + 1].kind == 1) { st[i].next_attn = 1; st[i].at = st[i + 1].at; }
     if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) {
         if (getenv("B2_MEGA_VERBOSE")) fprintf(stderr, "b2: persistent kernel not used: %s\n", last_error());
         cudaGetLastError();          // does not fit: keep the per-matrix path, and leave no stale CUDA error behind

@@ -435,7 +435,7 @@ __device__ __forceinline__ float gelu_f16_table(float v) {
 }
 
 static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best, int pos_value = -1,
-                                     const int* page_table_override = nullptr) {
+                                     const int* page_table_override = nullptr, bool ll_out = false) {
     if (a.bias) { v0 = __fadd_rn(v0, a.bias[r0]); v1 = __fadd_rn(v1, a.bias[r0 + 1]); }
     int epi = a.epi;
     if (epi == EPI_QKV_ROPE_GELU) {
@@ -445,7 +445,14 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
     }
     switch (epi) {
     case EPI_STORE: a.y[r0] = v0; a.y[r0 + 1] = v1; break;
-    case EPI_RESIDUAL: a.y[r0] = __fadd_rn(a.y[r0], v0); a.y[r0 + 1] = __fadd_rn(a.y[r0 + 1], v1); break;
+    case EPI_RESIDUAL: {
+        const float n0 = __fadd_rn(a.y[r0], v0), n1 = __fadd_rn(a.y[r0 + 1], v1);
+        a.y[r0] = n0; a.y[r0 + 1] = n1;
+        if (ll_out) {                                            // the next stage of the persistent kernel polls these
+            ll_store2(a.y_ll + r0, n0, n1);
+            ll_store2(a.y_ll_poison + r0, __uint_as_float(LL_POISON), __uint_as_float(LL_POISON));
+        }
+    } break;
     case EPI_RESIDUAL2:
         a.y[r0] = __fadd_rn(__fadd_rn(v0, a.y2[r0]), a.y[r0]);
         a.y[r0 + 1] = __fadd_rn(__fadd_rn(v1, a.y2[r0 + 1]), a.y[r0 + 1]);

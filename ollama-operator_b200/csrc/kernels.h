@@ -41,6 +41,13 @@ struct GemvArgs {
     QMat W;
     int pro = PRO_PLAIN, epi = EPI_STORE;
     const float* x = nullptr;      // [K]
+    // persistent kernel only: hand-over copies of a vector passed from one stage to the next.  Such a buffer holds the
+    // bit pattern LL_POISON (a NaN no arithmetic produces) in every word until the producing stage stores the value, so a
+    // reader that polls the words needs no grid barrier.  Two buffers alternate; whoever writes row r of one restores the
+    // poison in row r of the other, whose readers are provably done by then (mega.cu has the argument).
+    const float* x_ll = nullptr;   // [K] hand-over copy of x, written by the previous stage
+    float* y_ll = nullptr;         // [rows] the same for this stage's output (EPI_RESIDUAL) ...
+    float* y_ll_poison = nullptr;  // ... and the buffer of the alternate write, re-poisoned row by row
     const float* gain = nullptr;   // [K]  norm gain
     const float* nbias = nullptr;  // [K]  layer-norm bias
     float eps = 0.f;
@@ -69,6 +76,8 @@ size_t gemv_weight_bytes(const QMat& W);
 struct AttnArgs {
     const float* q = nullptr;          // [n_head][head_dim] f32 (rounded to f16 inside, as ggml does)
     float* out = nullptr;              // [n_head][head_dim] f32
+    float* out_ll = nullptr;           // persistent kernel: hand-over copy of out, and the alternate buffer to re-poison (see GemvArgs::x_ll)
+    float* out_ll_poison = nullptr;
     const __half* k_base = nullptr;    // [n_pages][page_tokens][kv_dim]
     const __half* v_base = nullptr;
     const int* page_table = nullptr;
@@ -107,6 +116,8 @@ struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident i
     int pairs_base = 0, pairs_rem = 0;   // row pairs per CTA; the first pairs_rem CTAs take one more
     int inv_S = 65536, inv_PT = 65536;   // ceil(2^16 / S), ceil(2^16 / PT): x / S == (x * inv_S) >> 16 for the small x used
     uint32_t arrive_units = 0;           // MEGA_EMPTY_BASE / (PT * S)
+    int ll_in = 0;                       // the input vector arrives through a hand-over buffer (g.x_ll): poll it instead of waiting at the grid barrier
+    int next_attn = 0;                   // an attention stage follows; `at` holds its arguments (for the KV prefetch)
     AttnArgs at;
     int att_max_local = 0;
     int tp_buf = 0, tp_n = 0;     // kind 2: which partial-sum buffer, vector length
@@ -116,6 +127,8 @@ struct MegaLaunch {
     const MegaStage* stages = nullptr;   // device array
     int s_begin = 0, s_end = 0;
     unsigned* grid_count = nullptr;      // zeroed before every launch
+    float* ll_init[2] = {nullptr, nullptr};   // hand-over buffers the first writers of a launch use: poisoned at kernel start
+    int ll_init_n[2] = {0, 0};
     unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
     const int* pos = nullptr;            // device scalar: position of the token being decoded
     const int* page_table = nullptr;     // this slot's page table

@@ -16,6 +16,8 @@
 //     cluster takes KV heads round-robin and exchanges max / sum / partial outputs through DSMEM
 //     (attn_dev.cuh), signalling with remote mbarrier arrives so the producer warp is not involved.
 // The kernel is launched cooperatively (all CTAs must be co-resident for the grid barrier).
+#include <type_traits>
+
 #include "attn_dev.cuh"
 #include "common.cuh"
 #include "formats.cuh"
@@ -106,7 +108,7 @@ __device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf,
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
                                                                    const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages,
-                                                                   const __grid_constant__ TpPeers tp) {
+                                                                   const __grid_constant__ TpPeers tp, float* ll_init0, int ll_n0, float* ll_init1, int ll_n1) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MEGA_NS_MAX;
@@ -228,8 +230,15 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     uint32_t ring_slot = 0, ring_phase = 0, xphase = 0;      // ring position of the next stage's first tile
     unsigned epoch = 0;
     unsigned tp_epoch = TP ? *reinterpret_cast<volatile unsigned*>(tp.epoch) : 0u;      // exchanges completed before this launch
+    // Hand-over buffers (GemvArgs::x_ll): every write w of a vector goes to buffer w % 2, and the thread that stores row r
+    // of write w puts the poison back into row r of the other buffer.  That buffer held write w - 1, whose readers (the
+    // prologue of the stage after it) have all finished: the writer of w is past its own prologue, which needed every
+    // CTA's output of the stage before, i.e. every CTA had left that earlier prologue.  The poison is visible before the
+    // next poll of that buffer because at least one grid barrier (QKV -> attention, up -> down) lies in between.  The
+    // buffers the first writers of a launch use are poisoned here, ahead of the first grid barrier.
+    for (int i = blockIdx.x * ntc + tid; i < ll_n0; i += gridDim.x * ntc) ll_store(ll_init0 + i, __uint_as_float(LL_POISON));
+    for (int i = blockIdx.x * ntc + tid; i < ll_n1; i += gridDim.x * ntc) ll_store(ll_init1 + i, __uint_as_float(LL_POISON));
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
-    constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
     for (int st = s_begin; st < s_end; st++) {
         const int db = (st - s_begin) & 1;
         mbar_wait(&dbar[db], (uint32_t)((st - s_begin) >> 1) & 1u);
@@ -265,6 +274,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             AttnCfg ac;
             ac.cluster = cluster_size;
             ac.max_local = S.att_max_local;
+            ac.ll_out = a.out_ll != nullptr;
             if (GRP > 1 && 2 * a.n_head_kv <= n_clusters) {
                 // few KV heads (GQA under tensor parallelism): one query head per cluster instead of one group
                 for (int h = my_cluster; h < a.n_head; h += n_clusters)
@@ -281,35 +291,59 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const GemvArgs& a = S.g;
         const int Sw = S.S, NW = S.G, RT = S.RT, nunits = S.nunits, nbeff = S.nbeff;
         const int K = (int)a.W.k, nchunks = K >> 2;
+        constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
         const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 127) == 0;
-        // the norm gain does not depend on the previous stage: fetch it while waiting at the barrier
-        float4 gv[MAXC];
-        if (fast && a.pro == PRO_RMSNORM) {
-#pragma unroll
-            for (int c = 0; c < MAXC; c++) {
-                const int i = tid + c * ntc;
-                gv[c] = i < nchunks ? *reinterpret_cast<const float4*>(a.gain + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        // ll_in: the input vector carries the producing stage's tag next to every value; polling those replaces the barrier
+        // (and the next descriptor is fetched further down, once every thread of this CTA is known to have left the previous stage)
+        const bool ll_in = !TP && S.ll_in != 0 && fast;
+        auto stage_barrier = [&]() {
+            if (!ll_in) {
+                if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
+                fetch_next_desc();
             }
-        }
-        if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
-        fetch_next_desc();
-        if (tr) { tr[1] = global_ns(); tr[10] = (unsigned long long)clock64(); }
-
-        if (fast) {
-            // x once into registers (one L2 round trip), RMS statistics, Q8_0 quantisation -- the same
-            // arithmetic as gemvdev::prologue_stats / prologue_q8_0
-            float4 xv[MAXC];
+            if (tr) { tr[1] = global_ns(); tr[10] = (unsigned long long)clock64(); }
+        };
+        // Fast prologue, NC = chunks per thread (3 covers K <= 5760 with half the registers of 6): x once into registers (one L2
+        // round trip), RMS statistics, Q8_0 quantisation -- the same arithmetic as gemvdev::prologue_stats / prologue_q8_0
+        auto fast_prologue = [&](auto nc_tag, auto norm_tag) {
+            constexpr int NC = decltype(nc_tag)::value;
+            constexpr bool NORM = decltype(norm_tag)::value;     // RMS norm (gains held in registers) or plain quantisation
+            // the norm gain does not depend on the previous stage: fetch it while waiting for the input
+            float4 gv[NORM ? NC : 1];
+            if constexpr (NORM) {
 #pragma unroll
-            for (int c = 0; c < MAXC; c++) {
-                const int i = tid + c * ntc;
-                xv[c] = i < nchunks ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int c = 0; c < NC; c++) {
+                    const int i = tid + c * ntc;
+                    gv[c] = i < nchunks ? *reinterpret_cast<const float4*>(a.gain + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            stage_barrier();
+            float4 xv[NC];
+            if (ll_in) {
+#pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    const int i = tid + c * ntc;
+                    xv[c] = i < nchunks ? ll_load4(a.x_ll + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    const int i = tid + c * ntc;
+                    SpinGuard guard;                        // a producer that never writes becomes a trap, not a hung GPU
+                    while (!ll_ready(xv[c])) { xv[c] = ll_load4(a.x_ll + 4 * i); guard.tick(); }
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    const int i = tid + c * ntc;
+                    xv[c] = i < nchunks ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
             }
             if (tr) tr[4] = (unsigned long long)clock64();          // (x loads issued)
             float scale = 1.f;
-            if (a.pro == PRO_RMSNORM) {
+            if constexpr (NORM) {
                 double ss = 0;
 #pragma unroll
-                for (int c = 0; c < MAXC; c++) {
+                for (int c = 0; c < NC; c++) {
                     if (c * ntc >= nchunks) break;          // (the chunks past the vector are zeros: skipping them changes nothing)
                     ss += (double)__fmul_rn(xv[c].x, xv[c].x); ss += (double)__fmul_rn(xv[c].y, xv[c].y);
                     ss += (double)__fmul_rn(xv[c].z, xv[c].z); ss += (double)__fmul_rn(xv[c].w, xv[c].w);
@@ -325,11 +359,11 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             // full-mask shuffles (xor 1,2,4 stay inside the 8 lanes that own one 32-element block)
             const unsigned gmask = 0xffffffffu;
 #pragma unroll
-            for (int c = 0; c < MAXC; c++) {
+            for (int c = 0; c < NC; c++) {
                 const int i = tid + c * ntc;
                 if (i < nchunks) {
                     float4 v = xv[c];
-                    if (a.pro == PRO_RMSNORM) {
+                    if constexpr (NORM) {
                         v.x = __fmul_rn(__fmul_rn(v.x, scale), gv[c].x); v.y = __fmul_rn(__fmul_rn(v.y, scale), gv[c].y);
                         v.z = __fmul_rn(__fmul_rn(v.z, scale), gv[c].z); v.w = __fmul_rn(__fmul_rn(v.w, scale), gv[c].w);
                     }
@@ -354,13 +388,25 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     }
                 }
             }
+        };
+        if (fast) {
+            const bool norm = a.pro == PRO_RMSNORM;
+            if (nchunks <= 3 * ntc) {
+                if (norm) fast_prologue(std::integral_constant<int, 3>{}, std::true_type{});
+                else fast_prologue(std::integral_constant<int, 3>{}, std::false_type{});
+            } else {
+                if (norm) fast_prologue(std::integral_constant<int, MAXC>{}, std::true_type{});
+                else fast_prologue(std::integral_constant<int, MAXC>{}, std::false_type{});
+            }
         } else {
+            stage_barrier();
             const ProStats ps = prologue_stats(a, dscratch, tid, ntc);
             if (TYPE == T_Q4_0 || TYPE == T_Q8_0) prologue_q8_0(a, ps, xq, xd, xs, tid, ntc);
             else prologue_q8_K(a, ps, xq, xd, xs, tid, ntc);
         }
         if (tr) tr[7] = (unsigned long long)clock64();              // (quantised)
         named_bar_sync(1, ntc);
+        if (ll_in) fetch_next_desc();                               // every thread of this CTA is past the previous stage now
         if (tr) tr[8] = (unsigned long long)clock64();              // (block barrier)
 
         const int worker = (warp * S.inv_S) >> 16, ch = warp - worker * Sw;      // warp / Sw, warp % Sw (reciprocal from the host)
@@ -377,13 +423,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         if (tr) { tr[2] = global_ns(); tr[9] = (unsigned long long)clock64(); }
         // the attention stage that follows will read K/V rows that already exist: pull them into L2
         // now, while this stage streams its weights
-        bool next_is_attn = false;
-        if (st + 1 < s_end) {
-            mbar_wait(&dbar[db ^ 1], (uint32_t)((st + 1 - s_begin) >> 1) & 1u);      // issued a stage ago (or at kernel start)
-            next_is_attn = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->kind == 1;
-        }
-        if (next_is_attn && !(sm.debug & 16)) {
-            const AttnArgs& na = reinterpret_cast<const MegaStage*>(s_desc[db ^ 1])->at;
+        if (S.next_attn && !(sm.debug & 16)) {
+            const AttnArgs& na = S.at;                              // the host copied the next stage's arguments here
             for (int kvh = my_cluster; kvh < na.n_head_kv; kvh += n_clusters) attn_prefetch<GRP, HD, ntc>(na, cluster_size, kvh, tid, pos_now, s_pt);
         }
 
@@ -462,6 +503,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         {
             unsigned long long best = 0ull;
             const int npairs = (int)((r_end - r_begin) >> 1);
+            const bool ll_out = !TP && a.y_ll != nullptr;
             for (int p = tid; p < npairs; p += ntc) {
                 double d0 = 0.0, d1 = 0.0;
                 for (int k = 0; k < Sw; k++) { d0 += ysum[(size_t)(2 * p) * Sw + k]; d1 += ysum[(size_t)(2 * p + 1) * Sw + k]; }
@@ -469,7 +511,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     a.y64[a.epi_row0 + r_begin + 2 * p] = d0;
                     a.y64[a.epi_row0 + r_begin + 2 * p + 1] = d1;
                 } else {
-                    epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt);
+                    epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt, ll_out);
                 }
             }
         }
@@ -566,7 +608,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     at[1].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp, L.ll_init[0], L.ll_init_n[0], L.ll_init[1], L.ll_init_n[1]));
     return B2_OK;
 }
 
