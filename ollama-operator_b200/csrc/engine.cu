@@ -379,7 +379,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
                  o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
                  o_pos = carve(4), o_key = carve(8), o_gc = carve(4), o_out = carve((size_t)out_cap * 4),
-                 o_forced = carve((size_t)max_ctx * 4), o_xll = carve((size_t)E * 8), o_attll = carve((size_t)nq * 8);
+                 o_forced = carve((size_t)max_ctx * 4), o_xll = carve((size_t)E * 12), o_attll = carve((size_t)nq * 8), o_hll = carve((size_t)F * 8);
     const size_t slot_bytes = align_up(off, 256);
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
     B2_CUDA(cudaMemset(slot_mem, 0, slot_bytes * max_batch));
@@ -392,7 +392,9 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
         s.att = (float*)(b + o_att); s.att2 = (float*)(b + o_att2); s.h = (float*)(b + o_h); s.logits = (float*)(b + o_logits);
         s.d_pos = (int*)(b + o_pos); s.d_key = (unsigned long long*)(b + o_key);
         s.d_out = (int*)(b + o_out); s.d_forced = (int*)(b + o_forced); s.d_grid_count = (unsigned*)(b + o_gc);
-        s.x_ll[0] = (float*)(b + o_xll); s.x_ll[1] = s.x_ll[0] + E; s.att_ll[0] = (float*)(b + o_attll); s.att_ll[1] = s.att_ll[0] + nq;
+        s.x_ll[0] = (float*)(b + o_xll); s.x_ll[1] = s.x_ll[0] + E; s.x_ll[2] = s.x_ll[1] + E;
+        s.att_ll[0] = (float*)(b + o_attll); s.att_ll[1] = s.att_ll[0] + nq;
+        s.h_ll[0] = (float*)(b + o_hll); s.h_ll[1] = s.h_ll[0] + F;
     }
     // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (ggml_rope_cache_init with
     // ext_factor 0: theta_base starts at pos and is multiplied by freq_base^(-2/n_rot) once per pair; the angle is
@@ -657,7 +659,7 @@ int Model::setup_mega(Slot& s) {
     // Stage hand-overs through tagged values instead of a grid barrier (mega.cu, `ll_in`): where a GEMV stage of the fast
     // prologue path reads exactly the vector the stage before it wrote (attention -> wo, wo -> up, down -> next qkv).
     if (tp_size <= 1 && !getenv("B2_MEGA_NO_LL")) {
-        int wx = 0, wa = 0;          // writes of x / att so far in the step: write w uses buffer w % 2 and re-poisons the other
+        int wx = 0, wa = 0, wh = 0;  // writes of x / att / h so far in the step: write w uses buffer w % NB and re-poisons that of write w - 1
         for (size_t i = 1; i < st.size(); i++) {
             MegaStage& c = st[i];
             MegaStage& p = st[i - 1];
@@ -669,14 +671,25 @@ int Model::setup_mega(Slot& s) {
             if (p.kind == 1 && p.at.out == g.x && g.W.k == (int64_t)hp.n_head * hp.head_dim) {
                 p.at.out_ll = s.att_ll[wa & 1]; p.at.out_ll_poison = s.att_ll[(wa + 1) & 1]; c.g.x_ll = s.att_ll[wa & 1]; c.ll_in = 1; wa++;
             } else if (p.kind == 0 && p.g.epi == EPI_RESIDUAL && p.g.y == g.x && p.g.epi_row0 == 0 && p.g.W.rows == g.W.k && g.W.k == hp.n_embd) {
-                p.g.y_ll = s.x_ll[wx & 1]; p.g.y_ll_poison = s.x_ll[(wx + 1) & 1]; c.g.x_ll = s.x_ll[wx & 1]; c.ll_in = 1; wx++;
+                p.g.y_ll = s.x_ll[wx % 3]; p.g.y_ll_poison = s.x_ll[(wx + 2) % 3]; c.g.x_ll = s.x_ll[wx % 3]; c.ll_in = 1; wx++;
+            } else if (p.kind == 0 && p.g.epi == EPI_SILU_MUL && p.g.y == g.x && p.g.epi_row0 == 0 && p.g.W.rows == 2 * g.W.k && g.W.k == hp.n_ff &&
+                       getenv("B2_MEGA_LL_H")) {      // (measured: 650 tok/s with h handed over this way, 659 with the grid barrier kept there)
+                p.g.y_ll = s.h_ll[wh & 1]; p.g.y_ll_poison = s.h_ll[(wh + 1) & 1]; c.g.x_ll = s.h_ll[wh & 1]; c.ll_in = 1; wh++;
             }
         }
-        if (wx) { L.ll_init[0] = s.x_ll[0]; L.ll_init_n[0] = hp.n_embd; }
-        if (wa) { L.ll_init[1] = s.att_ll[0]; L.ll_init_n[1] = hp.n_head * hp.head_dim; }
+        if (wx) { L.ll_init.p[0] = s.x_ll[0]; L.ll_init.p[1] = s.x_ll[1]; L.ll_init.n[0] = L.ll_init.n[1] = hp.n_embd; }
+        if (wa) { L.ll_init.p[2] = s.att_ll[0]; L.ll_init.n[2] = hp.n_head * hp.head_dim; }
+        if (wh) { L.ll_init.p[3] = s.h_ll[0]; L.ll_init.n[3] = hp.n_ff; }
     }
     for (size_t i = 0; i + 1 < st.size(); i++)
         if (st[i].kind == 0 && st[i + 1].kind == 1) { st[i].next_attn = 1; st[i].at = st[i + 1].at; }
+    // per-thread epilogue state kept across layers: only where every such stage has the same rows (one split) and nobody else writes x
+    if (tp_size <= 1 && !getenv("B2_MEGA_NO_EPI_CACHE"))
+        for (MegaStage& m : st) {
+            if (m.kind != 0 || m.g.epi_row0 != 0 || m.g.bias) continue;
+            if (m.g.epi == EPI_RESIDUAL && m.g.y == s.x && m.g.W.rows == hp.n_embd) m.epi_cache = 1;
+            else if (m.g.epi == EPI_QKV_ROPE && m.g.W.rows == (int64_t)m.g.n_q + 2 * m.g.n_kv) m.epi_cache = 2;
+        }
     if (mega_configure(L, k_max, tile_max, rt_s_max, max_ctx) != B2_OK) {
         if (getenv("B2_MEGA_VERBOSE")) fprintf(stderr, "b2: persistent kernel not used: %s\n", last_error());
         cudaGetLastError();          // does not fit: keep the per-matrix path, and leave no stale CUDA error behind

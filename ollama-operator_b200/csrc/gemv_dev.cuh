@@ -434,8 +434,16 @@ __device__ __forceinline__ float gelu_f16_table(float v) {
     return __half2float(__float2half_rn(__fmul_rn(__fmul_rn(0.5f, t), __fadd_rn(1.0f, th))));
 }
 
+// What a thread of the persistent kernel keeps from layer to layer for "its" row pair (same rows in every layer): the
+// residual values it wrote last and the RoPE (cos, sin) of its pair -- both would otherwise be an L2 round trip per layer.
+struct EpiCache {
+    float* res = nullptr;        // shared-memory slot of 2 floats, or null
+    float2* rope = nullptr;      // shared-memory slot, or null
+    bool res_valid = false, rope_valid = false;
+};
+
 static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, float v1, unsigned long long& best, int pos_value = -1,
-                                     const int* page_table_override = nullptr, bool ll_out = false) {
+                                     const int* page_table_override = nullptr, bool ll_out = false, const EpiCache ec = EpiCache()) {
     if (a.bias) { v0 = __fadd_rn(v0, a.bias[r0]); v1 = __fadd_rn(v1, a.bias[r0 + 1]); }
     int epi = a.epi;
     if (epi == EPI_QKV_ROPE_GELU) {
@@ -446,8 +454,10 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
     switch (epi) {
     case EPI_STORE: a.y[r0] = v0; a.y[r0 + 1] = v1; break;
     case EPI_RESIDUAL: {
-        const float n0 = __fadd_rn(a.y[r0], v0), n1 = __fadd_rn(a.y[r0 + 1], v1);
+        const bool cached = ec.res && ec.res_valid;
+        const float n0 = __fadd_rn(cached ? ec.res[0] : a.y[r0], v0), n1 = __fadd_rn(cached ? ec.res[1] : a.y[r0 + 1], v1);
         a.y[r0] = n0; a.y[r0 + 1] = n1;
+        if (ec.res) { ec.res[0] = n0; ec.res[1] = n1; }
         if (ll_out) {                                            // the next stage of the persistent kernel polls these
             ll_store2(a.y_ll + r0, n0, n1);
             ll_store2(a.y_ll_poison + r0, __uint_as_float(LL_POISON), __uint_as_float(LL_POISON));
@@ -457,7 +467,11 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
         a.y[r0] = __fadd_rn(__fadd_rn(v0, a.y2[r0]), a.y[r0]);
         a.y[r0 + 1] = __fadd_rn(__fadd_rn(v1, a.y2[r0 + 1]), a.y[r0 + 1]);
         break;
-    case EPI_SILU_MUL: a.y[r0 >> 1] = __fmul_rn(__fdiv_rn(v0, __fadd_rn(1.0f, (float)exp((double)(-v0)))), v1); break;
+    case EPI_SILU_MUL: {
+        const float h = __fmul_rn(__fdiv_rn(v0, __fadd_rn(1.0f, (float)exp((double)(-v0)))), v1);
+        a.y[r0 >> 1] = h;
+        if (ll_out) { ll_store(a.y_ll + (r0 >> 1), h); ll_store(a.y_ll_poison + (r0 >> 1), __uint_as_float(LL_POISON)); }
+    } break;
     case EPI_GELU: a.y[r0] = gelu_f16_table(v0); a.y[r0 + 1] = gelu_f16_table(v1); break;
     case EPI_LOGITS: {
         a.y[r0] = v0; a.y[r0 + 1] = v1;
@@ -478,7 +492,8 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
         if (!is_q && !is_k) {
             if (a.rope_neox && e < a.n_rot) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
         } else if (e < a.n_rot) {
-            const float2 cs = a.rope_cs[(size_t)(pos_value >= 0 ? pos_value : *a.kv.pos) * (a.n_rot >> 1) + (e >> 1)];
+            const float2 cs = ec.rope && ec.rope_valid ? *ec.rope : a.rope_cs[(size_t)(pos_value >= 0 ? pos_value : *a.kv.pos) * (a.n_rot >> 1) + (e >> 1)];
+            if (ec.rope && !ec.rope_valid) *ec.rope = cs;
             o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
             o1 = __fadd_rn(__fmul_rn(v0, cs.y), __fmul_rn(v1, cs.x));
             if (a.rope_neox) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }

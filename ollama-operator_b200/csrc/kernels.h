@@ -43,10 +43,10 @@ struct GemvArgs {
     const float* x = nullptr;      // [K]
     // persistent kernel only: hand-over copies of a vector passed from one stage to the next.  Such a buffer holds the
     // bit pattern LL_POISON (a NaN no arithmetic produces) in every word until the producing stage stores the value, so a
-    // reader that polls the words needs no grid barrier.  Two buffers alternate; whoever writes row r of one restores the
-    // poison in row r of the other, whose readers are provably done by then (mega.cu has the argument).
+    // reader that polls the words needs no grid barrier.  Two or three buffers rotate; whoever writes row r of one restores
+    // the poison in row r of the buffer of the previous write, whose readers are provably done by then (mega.cu has the argument).
     const float* x_ll = nullptr;   // [K] hand-over copy of x, written by the previous stage
-    float* y_ll = nullptr;         // [rows] the same for this stage's output (EPI_RESIDUAL) ...
+    float* y_ll = nullptr;         // [rows] the same for this stage's output (EPI_RESIDUAL, EPI_SILU_MUL) ...
     float* y_ll_poison = nullptr;  // ... and the buffer of the alternate write, re-poisoned row by row
     const float* gain = nullptr;   // [K]  norm gain
     const float* nbias = nullptr;  // [K]  layer-norm bias
@@ -118,6 +118,7 @@ struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident i
     uint32_t arrive_units = 0;           // MEGA_EMPTY_BASE / (PT * S)
     int ll_in = 0;                       // the input vector arrives through a hand-over buffer (g.x_ll): poll it instead of waiting at the grid barrier
     int next_attn = 0;                   // an attention stage follows; `at` holds its arguments (for the KV prefetch)
+    int epi_cache = 0;                   // 1: EPI_RESIDUAL on the residual stream, 2: the fused QKV matrix -- per-thread state kept across layers (gemvdev::EpiCache)
     AttnArgs at;
     int att_max_local = 0;
     int tp_buf = 0, tp_n = 0;     // kind 2: which partial-sum buffer, vector length
@@ -127,8 +128,8 @@ struct MegaLaunch {
     const MegaStage* stages = nullptr;   // device array
     int s_begin = 0, s_end = 0;
     unsigned* grid_count = nullptr;      // zeroed before every launch
-    float* ll_init[2] = {nullptr, nullptr};   // hand-over buffers the first writers of a launch use: poisoned at kernel start
-    int ll_init_n[2] = {0, 0};
+    struct LlInit { float* p[4] = {nullptr, nullptr, nullptr, nullptr}; int n[4] = {0, 0, 0, 0}; };
+    LlInit ll_init;                      // hand-over buffers the first writers of a launch use: poisoned at kernel start
     unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
     const int* pos = nullptr;            // device scalar: position of the token being decoded
     const int* page_table = nullptr;     // this slot's page table

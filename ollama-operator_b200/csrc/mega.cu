@@ -108,7 +108,7 @@ __device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf,
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
                                                                    const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages,
-                                                                   const __grid_constant__ TpPeers tp, float* ll_init0, int ll_n0, float* ll_init1, int ll_n1) {
+                                                                   const __grid_constant__ TpPeers tp, const MegaLaunch::LlInit ll_init) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MEGA_NS_MAX;
@@ -133,6 +133,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     // of them in dependent steps (barrier -> operands -> strides -> loop bounds).  Each stage's descriptor is
     // therefore copied into shared memory one stage ahead (bulk async copy, completion on dbar).
     __shared__ __align__(16) uint8_t s_desc[2][sizeof(MegaStage)];
+    // per-thread state kept from layer to layer (gemvdev::EpiCache): thread p of the epilogue owns the same row pair in every layer
+    constexpr int EPI_CACHE_PAIRS = 128;
+    __shared__ float s_res[2 * EPI_CACHE_PAIRS];
+    __shared__ float2 s_rope[EPI_CACHE_PAIRS];
     __shared__ uint64_t dbar[2];
     for (int i = tid; i < n_pages; i += blockDim.x) s_pt[i] = page_table[i];
     if (tid == 0) s_pos = *pos_ptr;
@@ -230,15 +234,20 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     uint32_t ring_slot = 0, ring_phase = 0, xphase = 0;      // ring position of the next stage's first tile
     unsigned epoch = 0;
     unsigned tp_epoch = TP ? *reinterpret_cast<volatile unsigned*>(tp.epoch) : 0u;      // exchanges completed before this launch
-    // Hand-over buffers (GemvArgs::x_ll): every write w of a vector goes to buffer w % 2, and the thread that stores row r
-    // of write w puts the poison back into row r of the other buffer.  That buffer held write w - 1, whose readers (the
-    // prologue of the stage after it) have all finished: the writer of w is past its own prologue, which needed every
-    // CTA's output of the stage before, i.e. every CTA had left that earlier prologue.  The poison is visible before the
-    // next poll of that buffer because at least one grid barrier (QKV -> attention, up -> down) lies in between.  The
-    // buffers the first writers of a launch use are poisoned here, ahead of the first grid barrier.
-    for (int i = blockIdx.x * ntc + tid; i < ll_n0; i += gridDim.x * ntc) ll_store(ll_init0 + i, __uint_as_float(LL_POISON));
-    for (int i = blockIdx.x * ntc + tid; i < ll_n1; i += gridDim.x * ntc) ll_store(ll_init1 + i, __uint_as_float(LL_POISON));
+    // Hand-over buffers (GemvArgs::x_ll): write number w of a vector goes to buffer w % NB of its rotation, and the thread
+    // that stores row r of write w puts the poison back into row r of the buffer of write w - 1.
+    //  * Nobody reads that buffer any more: its readers are the prologue of the stage after write w - 1, and the writer
+    //    of w is past its own prologue (or the QKV -> attention barrier), which needed every CTA's output of a stage after
+    //    that prologue.
+    //  * The poison is visible before that buffer is polled again (for write w - 1 + NB): the QKV -> attention grid
+    //    barrier of the next layer lies in between.  att and h are written once per layer (NB = 2 is enough); x is
+    //    written twice (by wo and down), so its rotation has NB = 3 buffers to put a barrier between poison and poll.
+    //  * The buffers of the first NB - 1 writes of a launch are poisoned here, ahead of the first grid barrier.
+#pragma unroll
+    for (int b = 0; b < 4; b++)
+        for (int i = blockIdx.x * ntc + tid; i < ll_init.n[b]; i += gridDim.x * ntc) ll_store(ll_init.p[b] + i, __uint_as_float(LL_POISON));
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
+    bool res_valid = false, rope_valid = false;          // the caches above hold this launch's values
     for (int st = s_begin; st < s_end; st++) {
         const int db = (st - s_begin) & 1;
         mbar_wait(&dbar[db], (uint32_t)((st - s_begin) >> 1) & 1u);
@@ -329,7 +338,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                 for (int c = 0; c < NC; c++) {
                     const int i = tid + c * ntc;
                     SpinGuard guard;                        // a producer that never writes becomes a trap, not a hung GPU
-                    while (!ll_ready(xv[c])) { xv[c] = ll_load4(a.x_ll + 4 * i); guard.tick(); }
+                    while (!ll_ready(xv[c])) { xv[c] = ll_load4(a.x_ll + 4 * i); guard.tick(); }      // (any __nanosleep here costs 10-20 %)
                 }
             } else {
 #pragma unroll
@@ -511,9 +520,16 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     a.y64[a.epi_row0 + r_begin + 2 * p] = d0;
                     a.y64[a.epi_row0 + r_begin + 2 * p + 1] = d1;
                 } else {
-                    epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt, ll_out);
+                    EpiCache ec;
+                    if (!TP && p < EPI_CACHE_PAIRS) {
+                        if (S.epi_cache == 1) { ec.res = s_res + 2 * p; ec.res_valid = res_valid; }
+                        else if (S.epi_cache == 2) { ec.rope = s_rope + p; ec.rope_valid = rope_valid; }
+                    }
+                    epilogue_pair(a, a.epi_row0 + r_begin + 2 * p, (float)d0, (float)d1, best, pos_now, s_pt, ll_out, ec);
                 }
             }
+            if (S.epi_cache == 1) res_valid = true;
+            else if (S.epi_cache == 2) rope_valid = true;
         }
         if (tr) tr[3] = global_ns();
     }
@@ -608,7 +624,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     at[1].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp, L.ll_init[0], L.ll_init_n[0], L.ll_init[1], L.ll_init_n[1]));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp, L.ll_init));
     return B2_OK;
 }
 
