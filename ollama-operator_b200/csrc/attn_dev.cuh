@@ -327,13 +327,9 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
             for (int w = 0; w < NWARP; w++) S += wsum[w * GRP + g];
             inv[g] = (float)(1.0 / S);                  // ggml: sum = 1.0/sum in f64, then an f32 scale
         }
-        for (int t = tid; t < n; t += NT) {
-#pragma unroll
-            for (int g = 0; g < GRP; g++)
-                sc[(size_t)g * maxc + t] = __half2float(__float2half_rn(__fmul_rn(sc[(size_t)g * maxc + t], inv[g])));
-        }
-        named_bar_sync(barid, NT);
     }
+    // the scaling by 1/sum and the rounding to f16 happen where the P.V product reads a probability (one pass and one barrier less)
+    auto prob = [&](int g, int t) { return __half2float(__float2half_rn(__fmul_rn(sc[(size_t)g * maxc + t], inv[g]))); };
     stamp(4);
 
     // ---- 3. output dims of this CTA: V columns dotted with the probabilities ------------------------------
@@ -373,7 +369,7 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
                         for (int j = 0; j < 4; j++) { const float2 f = __half22float2(h2[j]); vf[2 * j] = f.x; vf[2 * j + 1] = f.y; }
 #pragma unroll
                         for (int g = 0; g < GRP; g++) {
-                            const float p = sc[(size_t)g * maxc + t];
+                            const float p = prob(g, t);
 #pragma unroll
                             for (int j = 0; j < 8; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
                         }
@@ -431,7 +427,7 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
                     for (int j = 0; j < 4; j++) { const float2 f = __half22float2(h2[j]); vf[2 * j] = f.x; vf[2 * j + 1] = f.y; }
 #pragma unroll
                     for (int g = 0; g < GRP; g++) {
-                        const float p = sc[(size_t)g * maxc + t];
+                        const float p = prob(g, t);
 #pragma unroll
                         for (int j = 0; j < 8; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
                     }
