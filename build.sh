@@ -5,7 +5,7 @@ cd "$(dirname "$0")/ollama-operator_b200/csrc"
 OUT=../libb200gguf.so
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function
-       --fmad=true -Xptxas -v -ccbin /usr/bin/g++)
+       --fmad=true -Xptxas -v -ccbin /usr/bin/g++ ${B2_CXXFLAGS:-})
 mkdir -p ../build
 objs=()
 for f in dequant.cu gemv.cu attn.cu mega.cu batch.cu gemm.cu gemm_tc.cu step.cu engine.cu engine_batch.cu tp.cu api.cu noalloc.cu gguf.cpp tokenizer.cpp tokenizer_api.cpp store.cpp; do

@@ -102,7 +102,10 @@ struct TpPeers {
 int tp_allreduce_residual_launch(const TpPeers& p, int buf, float* x, int n, cudaStream_t st, bool pdl);
 
 // ---- mega.cu: the persistent decode kernel (all layers of a step in one launch) ---------------------
-constexpr int MEGA_NCW = 15;      // consumer warps per CTA
+#ifndef B2_MEGA_NCW
+#define B2_MEGA_NCW 15
+#endif
+constexpr int MEGA_NCW = B2_MEGA_NCW;      // consumer warps per CTA
 struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident in device memory (copied to shared memory by 16-byte bulk copies)
     int kind = 0;                 // 0 = GEMV, 1 = attention, 2 = tensor-parallel exchange (all-reduce + residual)
     GemvArgs g;

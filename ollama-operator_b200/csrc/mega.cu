@@ -300,7 +300,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const GemvArgs& a = S.g;
         const int Sw = S.S, NW = S.G, RT = S.RT, nunits = S.nunits, nbeff = S.nbeff;
         const int K = (int)a.W.k, nchunks = K >> 2;
-        constexpr int MAXC = 6;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
+        constexpr int MAXC = 8;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
         const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 127) == 0;
         // ll_in: the input vector carries the producing stage's tag next to every value; polling those replaces the barrier
         // (and the next descriptor is fetched further down, once every thread of this CTA is known to have left the previous stage)
@@ -403,6 +403,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             if (nchunks <= 3 * ntc) {
                 if (norm) fast_prologue(std::integral_constant<int, 3>{}, std::true_type{});
                 else fast_prologue(std::integral_constant<int, 3>{}, std::false_type{});
+            } else if (nchunks <= 6 * ntc) {
+                if (norm) fast_prologue(std::integral_constant<int, 6>{}, std::true_type{});
+                else fast_prologue(std::integral_constant<int, 6>{}, std::false_type{});
             } else {
                 if (norm) fast_prologue(std::integral_constant<int, MAXC>{}, std::true_type{});
                 else fast_prologue(std::integral_constant<int, MAXC>{}, std::false_type{});
@@ -583,7 +586,7 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
     size_t rb = 0;
     for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
     int pt = (int)((size_t)mega_tile_target() / (2 * rb));
-    pt = std::max(1, std::min(pt, std::max(1, 15 / st.S)));
+    pt = std::max(1, std::min(pt, std::max(1, ncw / st.S)));
     st.PT = pt;
     st.RT = 2 * pt;
     st.P = 1; st.RPG = 0;
