@@ -105,7 +105,9 @@ __device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf,
     }
 }
 
-template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
+// TRACE: the per-stage timestamps of b2_mega_trace are compiled into a variant of their own, so that the kernel that serves
+// requests carries neither their registers nor their branches (it sits at the 128-register limit of its 512 threads)
+template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP, bool TRACE = false>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
                                                                    const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages,
                                                                    const __grid_constant__ TpPeers tp, const MegaLaunch::LlInit ll_init) {
@@ -260,7 +262,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             }
         };
         // optional per-stage timestamps (ns): [0] stage entered, [1] barrier passed, [2] prologue done, [3] stage done
-        unsigned long long* tr = trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 16 : nullptr;
+        unsigned long long* tr = TRACE && trace && tid == 0 ? trace + ((size_t)blockIdx.x * (s_end - s_begin) + (st - s_begin)) * 16 : nullptr;
         if (tr) tr[0] = global_ns();
 
         if (TP && S.kind == 2) {
@@ -606,9 +608,10 @@ void mega_finish_stage(MegaStage& st, int grid) {
 
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
 static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
-    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD, TP>;
-    static PerDeviceSmem configured;
-    if (configured.raise(L.smem_bytes)) {
+    auto kern = mega_kernel<TYPE, NB, NCW, GRP, HD, TP, false>;
+    if (!TP && L.trace) kern = mega_kernel<TYPE, NB, NCW, GRP, HD, false, !TP>;      // (no traced variant under tensor parallelism)
+    static PerDeviceSmem configured[2];
+    if (configured[L.trace ? 1 : 0].raise(L.smem_bytes)) {
         B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
         B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
     }
