@@ -665,7 +665,7 @@ int Model::setup_mega(Slot& s) {
             MegaStage& p = st[i - 1];
             if (c.kind != 0) continue;
             const GemvArgs& g = c.g;
-            const bool fast = (g.W.type == T_Q4_0 || g.W.type == T_Q8_0) && (g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 128 == 0 &&
+            const bool fast = (g.W.type == T_Q4_0 || g.W.type == T_Q8_0) && (g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 256 == 0 &&
                               g.W.k / 4 <= (int64_t)8 * MEGA_NCW * 32;          // the kernel's fast prologue path (mega.cu)
             if (!fast) continue;
             if (p.kind == 1 && p.at.out == g.x && g.W.k == (int64_t)hp.n_head * hp.head_dim) {

@@ -303,7 +303,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const int Sw = S.S, NW = S.G, RT = S.RT, nunits = S.nunits, nbeff = S.nbeff;
         const int K = (int)a.W.k, nchunks = K >> 2;
         constexpr int MAXC = 8;                               // float4 chunks of x per thread held in registers (K <= 4*ntc*MAXC)
-        const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 127) == 0;
+        const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 255) == 0;
         // ll_in: the input vector carries the producing stage's tag next to every value; polling those replaces the barrier
         // (and the next descriptor is fetched further down, once every thread of this CTA is known to have left the previous stage)
         const bool ll_in = !TP && S.ll_in != 0 && fast;
@@ -314,39 +314,45 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             }
             if (tr) { tr[1] = global_ns(); tr[10] = (unsigned long long)clock64(); }
         };
-        // Fast prologue, NC = chunks per thread (3 covers K <= 5760 with half the registers of 6): x once into registers (one L2
-        // round trip), RMS statistics, Q8_0 quantisation -- the same arithmetic as gemvdev::prologue_stats / prologue_q8_0
-        auto fast_prologue = [&](auto nc_tag, auto norm_tag) {
-            constexpr int NC = decltype(nc_tag)::value;
+        // Fast prologue: x once into registers (one L2 round trip), RMS statistics, Q8_0 quantisation -- the arithmetic of
+        // gemvdev::prologue_stats / prologue_q8_0.  A thread owns "octets" of 8 consecutive values (octet o = tid + k * ntc,
+        // k < NO), four lanes share a 32-value block: per value that is half the shuffles, divisions and address arithmetic of
+        // a 4-value mapping, and this phase is bound by the instructions the fifteen warps issue.
+        auto fast_prologue = [&](auto no_tag, auto norm_tag) {
+            constexpr int NO = decltype(no_tag)::value;
             constexpr bool NORM = decltype(norm_tag)::value;     // RMS norm (gains held in registers) or plain quantisation
+            const int noct = K >> 3;
             // the norm gain does not depend on the previous stage: fetch it while waiting for the input
-            float4 gv[NORM ? NC : 1];
+            float4 gv[NORM ? 2 * NO : 1];
             if constexpr (NORM) {
 #pragma unroll
-                for (int c = 0; c < NC; c++) {
-                    const int i = tid + c * ntc;
-                    gv[c] = i < nchunks ? *reinterpret_cast<const float4*>(a.gain + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = 0; k < NO; k++) {
+                    const int o = tid + k * ntc;
+                    gv[2 * k] = o < noct ? *reinterpret_cast<const float4*>(a.gain + 8 * o) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    gv[2 * k + 1] = o < noct ? *reinterpret_cast<const float4*>(a.gain + 8 * o + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
             stage_barrier();
-            float4 xv[NC];
+            float4 xv[2 * NO];
             if (ll_in) {
 #pragma unroll
-                for (int c = 0; c < NC; c++) {
-                    const int i = tid + c * ntc;
-                    xv[c] = i < nchunks ? ll_load4(a.x_ll + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = 0; k < NO; k++) {
+                    const int o = tid + k * ntc;
+                    xv[2 * k] = o < noct ? ll_load4(a.x_ll + 8 * o) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xv[2 * k + 1] = o < noct ? ll_load4(a.x_ll + 8 * o + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
 #pragma unroll
-                for (int c = 0; c < NC; c++) {
-                    const int i = tid + c * ntc;
+                for (int c = 0; c < 2 * NO; c++) {
+                    const int o = tid + (c >> 1) * ntc;
                     SpinGuard guard;                        // a producer that never writes becomes a trap, not a hung GPU
-                    while (!ll_ready(xv[c])) { xv[c] = ll_load4(a.x_ll + 4 * i); guard.tick(); }      // (any __nanosleep here costs 10-20 %)
-                }
+                    while (!ll_ready(xv[c])) { xv[c] = ll_load4(a.x_ll + 8 * o + 4 * (c & 1)); guard.tick(); }      // (any __nanosleep here costs 10-20 %;
+                }                                                                                                    //  polling all pending chunks at once: 2 % slower)
             } else {
 #pragma unroll
-                for (int c = 0; c < NC; c++) {
-                    const int i = tid + c * ntc;
-                    xv[c] = i < nchunks ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = 0; k < NO; k++) {
+                    const int o = tid + k * ntc;
+                    xv[2 * k] = o < noct ? __ldcg(reinterpret_cast<const float4*>(a.x + 8 * o)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xv[2 * k + 1] = o < noct ? __ldcg(reinterpret_cast<const float4*>(a.x + 8 * o + 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
             if (tr) tr[4] = (unsigned long long)clock64();          // (x loads issued)
@@ -354,8 +360,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             if constexpr (NORM) {
                 double ss = 0;
 #pragma unroll
-                for (int c = 0; c < NC; c++) {
-                    if (c * ntc >= nchunks) break;          // (the chunks past the vector are zeros: skipping them changes nothing)
+                for (int c = 0; c < 2 * NO; c++) {
+                    if ((c >> 1) * ntc >= noct) break;          // (the octets past the vector are zeros: skipping them changes nothing)
                     ss += (double)__fmul_rn(xv[c].x, xv[c].x); ss += (double)__fmul_rn(xv[c].y, xv[c].y);
                     ss += (double)__fmul_rn(xv[c].z, xv[c].z); ss += (double)__fmul_rn(xv[c].w, xv[c].w);
                 }
@@ -366,34 +372,37 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             }
             if (tr) tr[6] = (unsigned long long)clock64();          // (statistics reduced)
             const int nbk = K >> 5;
-            // K is a multiple of 128, so a warp's 32 chunks are all inside or all outside the vector:
-            // full-mask shuffles (xor 1,2,4 stay inside the 8 lanes that own one 32-element block)
+            // K is a multiple of 256, so a warp's 32 octets are all inside or all outside the vector:
+            // full-mask shuffles (xor 1, 2 stay inside the 4 lanes that own one 32-element block)
             const unsigned gmask = 0xffffffffu;
 #pragma unroll
-            for (int c = 0; c < NC; c++) {
-                const int i = tid + c * ntc;
-                if (i < nchunks) {
-                    float4 v = xv[c];
+            for (int k = 0; k < NO; k++) {
+                const int o = tid + k * ntc;
+                if (o < noct) {
+                    float4 v0 = xv[2 * k], v1 = xv[2 * k + 1];
                     if constexpr (NORM) {
-                        v.x = __fmul_rn(__fmul_rn(v.x, scale), gv[c].x); v.y = __fmul_rn(__fmul_rn(v.y, scale), gv[c].y);
-                        v.z = __fmul_rn(__fmul_rn(v.z, scale), gv[c].z); v.w = __fmul_rn(__fmul_rn(v.w, scale), gv[c].w);
+                        v0.x = __fmul_rn(__fmul_rn(v0.x, scale), gv[2 * k].x); v0.y = __fmul_rn(__fmul_rn(v0.y, scale), gv[2 * k].y);
+                        v0.z = __fmul_rn(__fmul_rn(v0.z, scale), gv[2 * k].z); v0.w = __fmul_rn(__fmul_rn(v0.w, scale), gv[2 * k].w);
+                        v1.x = __fmul_rn(__fmul_rn(v1.x, scale), gv[2 * k + 1].x); v1.y = __fmul_rn(__fmul_rn(v1.y, scale), gv[2 * k + 1].y);
+                        v1.z = __fmul_rn(__fmul_rn(v1.z, scale), gv[2 * k + 1].z); v1.w = __fmul_rn(__fmul_rn(v1.w, scale), gv[2 * k + 1].w);
                     }
-                    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+                    float amax = fmaxf(fmaxf(fmaxf(fabsf(v0.x), fabsf(v0.y)), fmaxf(fabsf(v0.z), fabsf(v0.w))),
+                                       fmaxf(fmaxf(fabsf(v1.x), fabsf(v1.y)), fmaxf(fabsf(v1.z), fabsf(v1.w))));
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 2));
-                    amax = fmaxf(amax, __shfl_xor_sync(gmask, amax, 4));
                     const float d = div127_rn(amax);
                     const float id = d != 0.0f ? __frcp_rn(d) : 0.0f;
-                    const int q0 = round_away_i(__fmul_rn(v.x, id)), q1 = round_away_i(__fmul_rn(v.y, id));
-                    const int q2 = round_away_i(__fmul_rn(v.z, id)), q3 = round_away_i(__fmul_rn(v.w, id));
-                    int sum = q0 + q1 + q2 + q3;
+                    const int q0 = round_away_i(__fmul_rn(v0.x, id)), q1 = round_away_i(__fmul_rn(v0.y, id));
+                    const int q2 = round_away_i(__fmul_rn(v0.z, id)), q3 = round_away_i(__fmul_rn(v0.w, id));
+                    const int q4 = round_away_i(__fmul_rn(v1.x, id)), q5 = round_away_i(__fmul_rn(v1.y, id));
+                    const int q6 = round_away_i(__fmul_rn(v1.z, id)), q7 = round_away_i(__fmul_rn(v1.w, id));
+                    int sum = ((q0 + q1) + (q2 + q3)) + ((q4 + q5) + (q6 + q7));
                     sum += __shfl_xor_sync(gmask, sum, 1);
                     sum += __shfl_xor_sync(gmask, sum, 2);
-                    sum += __shfl_xor_sync(gmask, sum, 4);
-                    const int bq = i >> 3, o = (i & 7) * 4;
-                    uint8_t* dst = xq + (o < 16 ? 0 : nbk * 16) + bq * 16 + (o & 15);
-                    *reinterpret_cast<uint32_t*>(dst) = pack4(q0, q1, q2, q3);
-                    if (o == 0) {
+                    const int bq = o >> 2, e0 = (o & 3) * 8;         // block, first element of the octet inside it
+                    uint8_t* dst = xq + (e0 < 16 ? 0 : nbk * 16) + bq * 16 + (e0 & 15);
+                    *reinterpret_cast<uint2*>(dst) = make_uint2(pack4(q0, q1, q2, q3), pack4(q4, q5, q6, q7));
+                    if (e0 == 0) {
                         xd[bq] = __half2float(__float2half_rn(d));
                         xs[bq] = 8 * sum;
                     }
@@ -402,15 +411,16 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         };
         if (fast) {
             const bool norm = a.pro == PRO_RMSNORM;
-            if (nchunks <= 3 * ntc) {
+            const int noct = K >> 3;
+            if (noct <= 2 * ntc) {
+                if (norm) fast_prologue(std::integral_constant<int, 2>{}, std::true_type{});
+                else fast_prologue(std::integral_constant<int, 2>{}, std::false_type{});
+            } else if (noct <= 3 * ntc) {
                 if (norm) fast_prologue(std::integral_constant<int, 3>{}, std::true_type{});
                 else fast_prologue(std::integral_constant<int, 3>{}, std::false_type{});
-            } else if (nchunks <= 6 * ntc) {
-                if (norm) fast_prologue(std::integral_constant<int, 6>{}, std::true_type{});
-                else fast_prologue(std::integral_constant<int, 6>{}, std::false_type{});
             } else {
-                if (norm) fast_prologue(std::integral_constant<int, MAXC>{}, std::true_type{});
-                else fast_prologue(std::integral_constant<int, MAXC>{}, std::false_type{});
+                if (norm) fast_prologue(std::integral_constant<int, MAXC / 2>{}, std::true_type{});
+                else fast_prologue(std::integral_constant<int, MAXC / 2>{}, std::false_type{});
             }
         } else {
             stage_barrier();
