@@ -3,6 +3,8 @@
 #pragma once
 #include <math.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -343,46 +345,63 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
         // Warp w owns chains c = w * rpw + lane / lpd; a chain stays in one thread, in position order, so the sums
         // are the ones the narrow layout below produces.  The 32 chain sums per dim meet in shared memory.
         float* pvs = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(rowoff + maxc) + 15) & ~(uintptr_t)15);        // [GRP][32 chains][dpc]
-        const int lpd = dpc >> 3, rpw = 32 / lpd;
+        // One query head (GRP = 1): 4 dims (8 bytes) per lane instead of 8 -- twice the warps share the work and a lane
+        // holds half the registers per row, which pays for more rows in flight (a context just past a multiple of 512
+        // would otherwise cost a second, exposed L2 round trip for one or two rows per chain).
+        auto pv_part = [&](auto dpl_tag) {
+        constexpr int DPL = decltype(dpl_tag)::value;           // dims per lane
+        const int lpd = dpc / DPL, rpw = 32 / lpd;
         if (warp < lpd) {
             const int dl = lane % lpd, c = warp * rpw + lane / lpd;
-            float acc[GRP][8];
+            float acc[GRP][DPL];
 #pragma unroll
             for (int g = 0; g < GRP; g++)
 #pragma unroll
-                for (int j = 0; j < 8; j++) acc[g][j] = 0.f;
-            constexpr int UV = GRP >= 4 ? 4 : GRP == 1 ? 16 : 8;        // V rows in flight per lane
+                for (int j = 0; j < DPL; j++) acc[g][j] = 0.f;
+            constexpr int UV = GRP >= 4 ? 4 : GRP > 1 ? 8 : DPL == 4 ? 20 : 16;        // V rows in flight per lane
             for (int tb = c; tb < n; tb += 32 * UV) {
-                uint4 vv[UV];
+                uint32_t vv[UV][DPL / 2];
 #pragma unroll
                 for (int u = 0; u < UV; u++) {
                     const int t = min(tb + 32 * u, n - 1);
-                    vv[u] = *reinterpret_cast<const uint4*>(v_base + rowoff[t] + dbase + dl * 8);
+                    const __half* src = v_base + rowoff[t] + dbase + dl * DPL;
+                    if constexpr (DPL == 8) {
+                        const uint4 q = *reinterpret_cast<const uint4*>(src);
+                        vv[u][0] = q.x; vv[u][1] = q.y; vv[u][DPL / 2 - 2] = q.z; vv[u][DPL / 2 - 1] = q.w;
+                    } else {
+                        const uint2 q = *reinterpret_cast<const uint2*>(src);
+                        vv[u][0] = q.x; vv[u][1] = q.y;
+                    }
                 }
 #pragma unroll
                 for (int u = 0; u < UV; u++) {
                     const int t = tb + 32 * u;
                     if (t < n) {
-                        const __half2* h2 = reinterpret_cast<const __half2*>(&vv[u]);
-                        float vf[8];
+                        float vf[DPL];
 #pragma unroll
-                        for (int j = 0; j < 4; j++) { const float2 f = __half22float2(h2[j]); vf[2 * j] = f.x; vf[2 * j + 1] = f.y; }
+                        for (int j = 0; j < DPL / 2; j++) {
+                            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&vv[u][j]));
+                            vf[2 * j] = f.x; vf[2 * j + 1] = f.y;
+                        }
 #pragma unroll
                         for (int g = 0; g < GRP; g++) {
                             const float p = prob(g, t);
 #pragma unroll
-                            for (int j = 0; j < 8; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
+                            for (int j = 0; j < DPL; j++) acc[g][j] = fmaf(vf[j], p, acc[g][j]);
                         }
                     }
                 }
             }
 #pragma unroll
             for (int g = 0; g < GRP; g++) {
-                float4* dst = reinterpret_cast<float4*>(pvs + ((size_t)g * 32 + c) * dpc + dl * 8);
+                float4* dst = reinterpret_cast<float4*>(pvs + ((size_t)g * 32 + c) * dpc + dl * DPL);
                 dst[0] = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
-                dst[1] = make_float4(acc[g][4], acc[g][5], acc[g][6], acc[g][7]);
+                if constexpr (DPL == 8) dst[1] = make_float4(acc[g][DPL - 4], acc[g][DPL - 3], acc[g][DPL - 2], acc[g][DPL - 1]);
             }
         }
+        };
+        if (GRP == 1 && dpc / 4 <= NWARP) pv_part(std::integral_constant<int, 4>{});
+        else pv_part(std::integral_constant<int, 8>{});
         named_bar_sync(barid, NT);
         for (int o = tid; o < GRP * dpc; o += NT) {
             const int g = o / dpc, d = o - g * dpc;
