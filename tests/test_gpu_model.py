@@ -255,3 +255,38 @@ def test_13b_width_tiles_smaller_than_a_worker_round(pkg, oracle, eng, model_dir
         got = [int(np.argmax(lg))] + [int(t) for t in m.decode_greedy(seq, 47)]
         assert got == want, (flags, next(i for i in range(48) if got[i] != want[i]))
         m.close()
+
+
+def test_stage_handover_without_grid_barriers_keeps_the_bits(pkg, oracle, eng, model_dir, monkeypatch):
+    """The persistent kernel hands x and the attention output from stage to stage through poisoned buffers that the
+    next stage polls (no grid barrier at attention->wo, wo->up, down->qkv).  A race there would show as a token or a
+    logit bit that differs from the same kernel with every grid barrier in place (B2_MEGA_NO_LL) -- over a few hundred
+    steps and two sequences that reuse the buffers of one slot after another -- or from the canonical oracle."""
+    path = pkg.synth.cached_model("wide-llama-2l", model_dir, source="blocks")
+    om = oracle.OracleModel(path, faithful=2)
+    toks = pkg.synth.prompt_tokens(40, om.m.n_vocab, seed=5)
+    want, _ = om.generate(toks, 32)
+    runs = {}
+    for name, env in (("handover", None), ("barriers", "1"), ("handover_h", "h")):
+        monkeypatch.delenv("B2_MEGA_NO_LL", raising=False)
+        monkeypatch.delenv("B2_MEGA_LL_H", raising=False)
+        if env == "1":
+            monkeypatch.setenv("B2_MEGA_NO_LL", "1")
+        if env == "h":
+            monkeypatch.setenv("B2_MEGA_LL_H", "1")          # also hand h over (off by default: slower, same bits)
+        m = eng.load(path, max_batch=2, max_ctx=384)
+        out = []
+        for rep in range(2):                                   # the second sequence reuses slot state the first one left
+            seq = m.seq_new()
+            lg = m.prefill(seq, toks)
+            got = [int(np.argmax(lg))] + [int(t) for t in m.decode_greedy(seq, 300)]
+            _, lgs = m.decode([seq], [got[-1]], want_logits=True)
+            out.append((got, lgs[0].view(np.uint32).copy()))
+            m.seq_free(seq)
+        m.close()
+        assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1]), name
+        runs[name] = out[0]
+    assert runs["handover"][0][:32] == want
+    for name in ("barriers", "handover_h"):
+        assert runs["handover"][0] == runs[name][0], name
+        assert np.array_equal(runs["handover"][1], runs[name][1]), name
