@@ -560,7 +560,7 @@ int g_mega_sms = 0;
 // Estimated consumer cost of a stage per row pair: (units per lane x 2 rows x ~27 instructions + the f64
 // butterfly, ~35) spread over the G row workers -- the model behind the choice of units per lane.
 static int mega_tile_target() {
-    static const int v = getenv("B2_MEGA_TILE_KB") ? atoi(getenv("B2_MEGA_TILE_KB")) * 1024 : 72 * 1024;
+    static const int v = getenv("B2_MEGA_TILE_KB") ? atoi(getenv("B2_MEGA_TILE_KB")) * 1024 : 60 * 1024;
     return v;
 }
 static double plan_cost(int nunits, int nbe, int ncw, int* S_out, int* G_out) {
@@ -593,8 +593,10 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
         if (c < best) { best = c; best_idle = 0; st.nbeff = nbe; st.S = S; st.G = G; }
     }
     if (best_idle == (1 << 30)) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: k=%lld does not map onto %d consumer warps", (long long)W.k, ncw);
-    // tile = PT row pairs, up to 72 KB (one bulk copy per plane: a single producer thread issues about three
-    // tiles per microsecond, so small tiles would bound the stream); PT * S owner warps (<= 15) release a tile
+    // tile = PT row pairs, up to 60 KB (one bulk copy per plane: a single producer thread issues about three
+    // tiles per microsecond, so small tiles would bound the stream; 60 KB lets three tiles fit next to the attention
+    // buffers of a short context -- 7B, ctx 512: 680 tok/s with 72 KB / two slots, 712 with 60 KB / three, 699 with
+    // 46 KB / four); PT * S owner warps (<= 15) release a tile
     size_t rb = 0;
     for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
     int pt = (int)((size_t)mega_tile_target() / (2 * rb));
