@@ -17,6 +17,7 @@ struct AttnCfg {
     int cluster;        // CTAs per (slot, kv head)
     int max_local;      // capacity of the score buffer: ALL positions of the sequence (every CTA holds them)
     bool ll_out = false;    // also write the hand-over copy a.out_ll and re-poison a.out_ll_poison (persistent kernel, see GemvArgs::x_ll)
+    bool ll_in = false;     // q and the current position's K/V rows arrive through a.qkv_ll (polled), not behind a grid barrier
 };
 
 // One all-to-all step between the CTAs of a cluster without involving threads outside the NT
@@ -166,7 +167,39 @@ static __device__ __noinline__ void attn_kv_head(const AttnArgs& a, const AttnCf
     float* wred = sc + (size_t)GRP * maxc;                           // [NWARP][GRP]
     int* rowoff = reinterpret_cast<int*>(wred + NWARP * GRP);        // [maxc] element offset of every cached row inside a layer's pool
 
-    for (int i = tid; i < GRP * HD; i += NT) qs[i] = __half2float(__float2half_rn(__ldcg(a.q + (size_t)kvh * GRP * HD + i)));
+    if (c.ll_in) {
+        // Hand-over from the QKV stage (no grid barrier in between): poll the query; and poll the new cache rows this CTA is
+        // going to read -- the K row if it scores the last position, its slice of the V row -- and store them into the cache
+        // itself.  The QKV stage stores the same bits there, but only a value seen in the hand-over buffer is known to have
+        // arrived; after the block barrier below the loops read the cache as for every other position.
+        const int kvi = kv_index >= 0 ? kv_index : kvh, nq = a.n_head * HD;
+        const uint32_t* words = reinterpret_cast<const uint32_t*>(a.qkv_ll) + nq;
+        const int last = n - 1, per0 = (n + CL - 1) / CL, dpc0 = HD / CL;
+        const bool own_k = last >= (int)rk * per0 && last < (int)rk * per0 + per0;
+        const size_t row = (size_t)((page_table[last >> pshift] << pshift) + (last & pmask)) * kv_dim;
+        for (int i = tid; i < GRP * HD + HD / 2 + dpc0 / 2; i += NT) {
+            SpinGuard guard;
+            if (i < GRP * HD) {
+                float v;
+                do { v = __uint_as_float(ll_load_u32(reinterpret_cast<const uint32_t*>(a.qkv_ll) + (size_t)kvh * GRP * HD + i)); guard.tick(); } while (__float_as_uint(v) == LL_POISON);
+                qs[i] = __half2float(__float2half_rn(v));
+            } else if (i < GRP * HD + HD / 2) {
+                if (own_k) {
+                    const int w = i - GRP * HD;
+                    uint32_t v;
+                    do { v = ll_load_u32(words + (size_t)kvi * (HD / 2) + w); guard.tick(); } while (v == LL_POISON);
+                    reinterpret_cast<uint32_t*>(const_cast<__half*>(k_base + row))[w] = v;
+                }
+            } else {
+                const int w = i - GRP * HD - HD / 2;
+                uint32_t v;
+                do { v = ll_load_u32(words + (a.kv_dim >> 1) + (size_t)kvi * (HD / 2) + (int)rk * (dpc0 / 2) + w); guard.tick(); } while (v == LL_POISON);
+                reinterpret_cast<uint32_t*>(const_cast<__half*>(v_base + row + (int)rk * dpc0))[w] = v;
+            }
+        }
+    } else {
+        for (int i = tid; i < GRP * HD; i += NT) qs[i] = __half2float(__float2half_rn(__ldcg(a.q + (size_t)kvh * GRP * HD + i)));
+    }
     // page-table walk once per position, in parallel, instead of inside the latency-bound loops below
     for (int t = tid; t < n; t += NT) rowoff[t] = ((page_table[t >> pshift] << pshift) + (t & pmask)) * kv_dim;
     named_bar_sync(barid, NT);

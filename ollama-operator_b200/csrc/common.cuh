@@ -74,6 +74,14 @@ __device__ __forceinline__ float4 ll_load4(const float* p) {                    
     asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void ll_store_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ll_load_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ bool ll_ready(const float4& v) {
     return __float_as_uint(v.x) != LL_POISON && __float_as_uint(v.y) != LL_POISON && __float_as_uint(v.z) != LL_POISON && __float_as_uint(v.w) != LL_POISON;
 }

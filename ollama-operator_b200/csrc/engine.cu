@@ -379,7 +379,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
     const size_t o_state = carve(sizeof(SeqState)), o_pt = carve((size_t)pages_per_seq * 4), o_x = carve((size_t)E * 4), o_q = carve((size_t)nq * 4),
                  o_att = carve((size_t)nq * 4), o_att2 = carve((size_t)E * 4), o_h = carve((size_t)F * 4), o_logits = carve((size_t)V * 4),
                  o_pos = carve(4), o_key = carve(8), o_gc = carve(4), o_out = carve((size_t)out_cap * 4),
-                 o_forced = carve((size_t)max_ctx * 4), o_xll = carve((size_t)E * 12), o_attll = carve((size_t)nq * 8), o_hll = carve((size_t)F * 8);
+                 o_forced = carve((size_t)max_ctx * 4), o_xll = carve((size_t)E * 12), o_attll = carve((size_t)nq * 8), o_hll = carve((size_t)F * 8), o_qkvll = carve((size_t)(nq + nkv) * 8);
     const size_t slot_bytes = align_up(off, 256);
     B2_CUDA(cudaMalloc(&slot_mem, slot_bytes * max_batch));
     B2_CUDA(cudaMemset(slot_mem, 0, slot_bytes * max_batch));
@@ -395,6 +395,7 @@ int Model::load(const char* path, const b2_load_opts* o, int rank, int size) {
         s.x_ll[0] = (float*)(b + o_xll); s.x_ll[1] = s.x_ll[0] + E; s.x_ll[2] = s.x_ll[1] + E;
         s.att_ll[0] = (float*)(b + o_attll); s.att_ll[1] = s.att_ll[0] + nq;
         s.h_ll[0] = (float*)(b + o_hll); s.h_ll[1] = s.h_ll[0] + F;
+        s.qkv_ll[0] = (float*)(b + o_qkvll); s.qkv_ll[1] = s.qkv_ll[0] + nq + nkv;      // [nq floats | nkv/2 words K | nkv/2 words V]
     }
     // RoPE (cos, sin) for every position, computed on the host exactly as ggml does (ggml_rope_cache_init with
     // ext_factor 0: theta_base starts at pos and is multiplied by freq_base^(-2/n_rot) once per pair; the angle is
@@ -659,10 +660,18 @@ int Model::setup_mega(Slot& s) {
     // Stage hand-overs through tagged values instead of a grid barrier (mega.cu, `ll_in`): where a GEMV stage of the fast
     // prologue path reads exactly the vector the stage before it wrote (attention -> wo, wo -> up, down -> next qkv).
     if (tp_size <= 1 && !getenv("B2_MEGA_NO_LL")) {
-        int wx = 0, wa = 0, wh = 0;  // writes of x / att / h so far in the step: write w uses buffer w % NB and re-poisons that of write w - 1
+        const int nkv_l = n_head_kv_l * hp.head_dim;
+        int wx = 0, wa = 0, wh = 0, wq = 0;  // writes of x / att / h / qkv so far in the step: write w uses buffer w % NB and re-poisons that of write w - 1
         for (size_t i = 1; i < st.size(); i++) {
             MegaStage& c = st[i];
             MegaStage& p = st[i - 1];
+            if (c.kind == 1 && p.kind == 0 && p.g.epi == EPI_QKV_ROPE && !p.g.rope_neox && p.g.epi_row0 == 0 && !p.g.bias && p.g.y == c.at.q &&
+                p.g.W.rows == (int64_t)p.g.n_q + 2 * p.g.n_kv && p.g.n_q == hp.n_head * hp.head_dim && p.g.n_kv == nkv_l && hp.head_dim % 2 == 0 &&
+                !getenv("B2_MEGA_NO_LL_QKV")) {
+                // qkv -> attention: the query and the current position's K/V rows (written in adjacent pairs by "norm" RoPE)
+                p.g.y_ll = s.qkv_ll[wq & 1]; p.g.y_ll_poison = s.qkv_ll[(wq + 1) & 1]; c.at.qkv_ll = s.qkv_ll[wq & 1]; c.ll_in = 1; wq++;
+                continue;
+            }
             if (c.kind != 0) continue;
             const GemvArgs& g = c.g;
             const bool fast = (g.W.type == T_Q4_0 || g.W.type == T_Q8_0) && (g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 256 == 0 &&
@@ -680,6 +689,7 @@ int Model::setup_mega(Slot& s) {
         if (wx) { L.ll_init.p[0] = s.x_ll[0]; L.ll_init.p[1] = s.x_ll[1]; L.ll_init.n[0] = L.ll_init.n[1] = hp.n_embd; }
         if (wa) { L.ll_init.p[2] = s.att_ll[0]; L.ll_init.n[2] = hp.n_head * hp.head_dim; }
         if (wh) { L.ll_init.p[3] = s.h_ll[0]; L.ll_init.n[3] = hp.n_ff; }
+        if (wq) { L.ll_init.p[4] = s.qkv_ll[0]; L.ll_init.n[4] = hp.n_head * hp.head_dim + nkv_l; }
     }
     for (size_t i = 0; i + 1 < st.size(); i++)
         if (st[i].kind == 0 && st[i + 1].kind == 1) { st[i].next_attn = 1; st[i].at = st[i + 1].at; }
@@ -730,6 +740,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
     {
         StepBeginArgs a;
         a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key; a.grid_count = s.d_grid_count;
+        if (s.mega_ok) a.ll_init = s.mega.ll_init;
         B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
     }
     if (s.mega_ok) {

@@ -52,7 +52,7 @@ struct Slot {
     unsigned long long* d_key = nullptr;
     int *d_out = nullptr, *d_forced = nullptr;
     unsigned* d_grid_count = nullptr;
-    float *x_ll[3] = {}, *att_ll[2] = {}, *h_ll[2] = {};      // hand-over copies of x, att and h for the persistent kernel (GemvArgs::x_ll)
+    float *x_ll[3] = {}, *att_ll[2] = {}, *h_ll[2] = {}, *qkv_ll[2] = {};      // hand-over copies of x, att and h for the persistent kernel (GemvArgs::x_ll)
     std::vector<StepOp> ops;       // the layer pipeline with this slot's buffers bound
     bool mega_ok = false;          // the persistent kernel can run this model
     MegaLaunch mega;

@@ -499,8 +499,13 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
             if (a.rope_neox) { i0 = e >> 1; i1 = (e >> 1) + a.n_rot / 2; }
         }
         if (is_q) {
-            a.y[hb + i0] = __fmul_rn(o0, a.q_scale);
-            a.y[hb + i1] = __fmul_rn(o1, a.q_scale);
+            const float q0 = __fmul_rn(o0, a.q_scale), q1 = __fmul_rn(o1, a.q_scale);
+            a.y[hb + i0] = q0;
+            a.y[hb + i1] = q1;
+            if (ll_out) {           // (the host sets y_ll for this epilogue only when i1 == i0 + 1: "norm" RoPE)
+                ll_store2(a.y_ll + hb + i0, q0, q1);
+                ll_store2(a.y_ll_poison + hb + i0, __uint_as_float(LL_POISON), __uint_as_float(LL_POISON));
+            }
         } else {
             const int pos = pos_value >= 0 ? pos_value : *a.kv.pos;
             const int page = (page_table_override ? page_table_override : a.kv.page_table)[pos / a.kv.page_tokens];
@@ -508,6 +513,12 @@ static __device__ void epilogue_pair(const GemvArgs& a, int64_t r0, float v0, fl
             __half* dst = (is_k ? a.kv.k_base : a.kv.v_base) + base + hb;
             dst[i0] = __float2half_rn(o0);
             dst[i1] = __float2half_rn(o1);
+            if (ll_out) {           // the same two halves as one word, where the attention stage polls for them
+                const uint32_t w = (uint32_t)__half_as_ushort(__float2half_rn(o0)) | ((uint32_t)__half_as_ushort(__float2half_rn(o1)) << 16);
+                const size_t wi = (size_t)a.n_q + (is_k ? 0 : (a.n_kv >> 1)) + ((hb + i0) >> 1);
+                ll_store_u32(reinterpret_cast<uint32_t*>(a.y_ll) + wi, w);
+                ll_store_u32(reinterpret_cast<uint32_t*>(a.y_ll_poison) + wi, LL_POISON);
+            }
         }
     } break;
     default: break;

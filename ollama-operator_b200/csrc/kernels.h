@@ -47,6 +47,8 @@ struct GemvArgs {
     // the poison in row r of the buffer of the previous write, whose readers are provably done by then (mega.cu has the argument).
     const float* x_ll = nullptr;   // [K] hand-over copy of x, written by the previous stage
     float* y_ll = nullptr;         // [rows] the same for this stage's output (EPI_RESIDUAL, EPI_SILU_MUL) ...
+                                   // EPI_QKV_ROPE: [n_q floats | n_kv/2 words of K | n_kv/2 words of V] -- the query and, as half2
+                                   // words, the new cache rows, for the attention stage that follows (AttnArgs::qkv_ll)
     float* y_ll_poison = nullptr;  // ... and the buffer of the alternate write, re-poisoned row by row
     const float* gain = nullptr;   // [K]  norm gain
     const float* nbias = nullptr;  // [K]  layer-norm bias
@@ -78,6 +80,8 @@ struct AttnArgs {
     float* out = nullptr;              // [n_head][head_dim] f32
     float* out_ll = nullptr;           // persistent kernel: hand-over copy of out, and the alternate buffer to re-poison (see GemvArgs::x_ll)
     float* out_ll_poison = nullptr;
+    const float* qkv_ll = nullptr;     // persistent kernel: hand-over copy of q and of the current position's K/V rows (GemvArgs::y_ll
+                                       // of the fused QKV stage); the attention polls it instead of waiting at a grid barrier
     const __half* k_base = nullptr;    // [n_pages][page_tokens][kv_dim]
     const __half* v_base = nullptr;
     const int* page_table = nullptr;
@@ -131,8 +135,8 @@ struct MegaLaunch {
     const MegaStage* stages = nullptr;   // device array
     int s_begin = 0, s_end = 0;
     unsigned* grid_count = nullptr;      // zeroed before every launch
-    struct LlInit { float* p[4] = {nullptr, nullptr, nullptr, nullptr}; int n[4] = {0, 0, 0, 0}; };
-    LlInit ll_init;                      // hand-over buffers the first writers of a launch use: poisoned at kernel start
+    struct LlInit { float* p[6] = {}; int n[6] = {}; };
+    LlInit ll_init;                      // hand-over buffers the first writers of a launch use: poisoned by the kernel before it (step_begin)
     unsigned long long* trace = nullptr; // optional [grid][stages][4] globaltimer stamps (debug)
     const int* pos = nullptr;            // device scalar: position of the token being decoded
     const int* page_table = nullptr;     // this slot's page table
@@ -169,6 +173,7 @@ struct StepBeginArgs {
     int* pos_out = nullptr;        // device scalar consumed by the layer kernels
     unsigned long long* argmax_key = nullptr;
     unsigned* grid_count = nullptr;   // persistent kernel's barrier counter, cleared every step (may be null)
+    MegaLaunch::LlInit ll_init;       // ... and the hand-over buffers its first writers use, poisoned every step
 };
 int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
 struct StepEndArgs {

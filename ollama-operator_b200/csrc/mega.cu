@@ -110,7 +110,7 @@ __device__ __noinline__ void tp_exchange(const TpPeers& tp, unsigned e, int buf,
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP, bool TRACE = false>
 __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage* __restrict__ stages, int s_begin, int s_end, unsigned* grid_count,
                                                                    const MegaSmem sm, unsigned long long* trace, const int* pos_ptr, const int* page_table, int n_pages,
-                                                                   const __grid_constant__ TpPeers tp, const MegaLaunch::LlInit ll_init) {
+                                                                   const __grid_constant__ TpPeers tp) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + MEGA_NS_MAX;
@@ -244,10 +244,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     //  * The poison is visible before that buffer is polled again (for write w - 1 + NB): the QKV -> attention grid
     //    barrier of the next layer lies in between.  att and h are written once per layer (NB = 2 is enough); x is
     //    written twice (by wo and down), so its rotation has NB = 3 buffers to put a barrier between poison and poll.
-    //  * The buffers of the first NB - 1 writes of a launch are poisoned here, ahead of the first grid barrier.
-#pragma unroll
-    for (int b = 0; b < 4; b++)
-        for (int i = blockIdx.x * ntc + tid; i < ll_init.n[b]; i += gridDim.x * ntc) ll_store(ll_init.p[b] + i, __uint_as_float(LL_POISON));
+    //  * The buffers of the first NB - 1 writes of a launch are poisoned by the kernel that precedes this one (step_begin).
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
     bool res_valid = false, rope_valid = false;          // the caches above hold this launch's values
     for (int st = s_begin; st < s_end; st++) {
@@ -277,7 +274,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             continue;
         }
         if (S.kind != 0) {
-            if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);
+            const bool att_ll = !TP && S.ll_in != 0;      // q and the new K/V rows come through a hand-over buffer (attn_dev.cuh)
+            if (att_ll) named_bar_sync(1, ntc);           // (every thread of this CTA has left the previous stage: its descriptor may go)
+            else if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);
             fetch_next_desc();
             if (tr) tr[1] = global_ns();
             // ---- attention: clusters take KV heads round-robin ----
@@ -286,6 +285,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             ac.cluster = cluster_size;
             ac.max_local = S.att_max_local;
             ac.ll_out = a.out_ll != nullptr;
+            ac.ll_in = att_ll;
             if (GRP > 1 && 2 * a.n_head_kv <= n_clusters) {
                 // few KV heads (GQA under tensor parallelism): one query head per cluster instead of one group
                 for (int h = my_cluster; h < a.n_head; h += n_clusters)
@@ -642,7 +642,7 @@ static int mega_launch_t(const MegaLaunch& L, cudaStream_t stream) {
     at[1].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp, L.ll_init));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, L.stages, L.s_begin, L.s_end, L.grid_count, sm, L.trace, L.pos, L.page_table, L.n_pages, L.tp));
     return B2_OK;
 }
 

@@ -17,6 +17,11 @@ __global__ void step_begin_kernel(const StepBeginArgs a) {
     const int tok = a.st->cur_tok, pos = a.st->pos;
     const int E = (int)a.embd.k;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < E; i += gridDim.x * blockDim.x) a.x[i] = qmat_elem(a.embd, tok, i);
+    // hand-over buffers of the persistent kernel (GemvArgs::x_ll): the ones written first in a step start out poisoned; done
+    // here, a whole kernel boundary ahead of the first value stored into them
+#pragma unroll
+    for (int b = 0; b < 6; b++)
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.ll_init.n[b]; i += gridDim.x * blockDim.x) a.ll_init.p[b][i] = __uint_as_float(LL_POISON);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *a.pos_out = pos;
         *a.argmax_key = 0ull;
