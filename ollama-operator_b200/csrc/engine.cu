@@ -718,6 +718,9 @@ int Model::setup_mega(Slot& s) {
     L.pf_bytes = 256u << 10;                        // x 132 CTAs = 34 MB of the 126 MB L2
     if (const char* v = getenv("B2_MEGA_PF_KB")) L.pf_bytes = (uint32_t)atoi(v) << 10;
     if (const char* v = getenv("B2_MEGA_DEBUG")) L.debug = atoi(v);
+    if (getenv("B2_MEGA_VERBOSE"))
+        fprintf(stderr, "b2: persistent kernel: %d CTAs (clusters of %d), %d ring slots of %u B after %u B of buffers, %zu B of shared memory\n", L.grid, L.cluster, L.ns,
+                L.stage_bytes, L.off_ring, L.smem_bytes);
     if (pages_per_seq > 256) return B2_OK;          // the kernel keeps the page table in shared memory
     s.mega_ok = true;
     return B2_OK;
