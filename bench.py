@@ -220,6 +220,7 @@ def run_gpu(args):
     info = m.info
     prompt = p.synth.prompt_tokens(args.ctx, info.n_vocab)
     seq = m.seq_new()
+    m.prefill(seq, prompt[:64]); m.seq_truncate(seq, 0)      # first launches of the batched kernels (module load, attributes) outside the timing
     logits0 = m.prefill(seq, prompt)
     prefill_ms = m.stats().gpu_ms
 
