@@ -122,7 +122,7 @@ struct alignas(16) MegaStage {    // one stage of the layer pipeline, resident i
     // filled in by mega_finish_stage once the grid is known, so that the kernel divides nothing per stage:
     int pairs_base = 0, pairs_rem = 0;   // row pairs per CTA; the first pairs_rem CTAs take one more
     int inv_S = 65536, inv_PT = 65536;   // ceil(2^16 / S), ceil(2^16 / PT): x / S == (x * inv_S) >> 16 for the small x used
-    uint32_t arrive_units = 0;           // MEGA_EMPTY_BASE / (PT * S)
+    uint32_t arrive_units = 0;           // MEGA_EMPTY_BASE / (G * S): every working warp arrives on a tile's `empty` barrier
     int ll_in = 0;                       // the input vector arrives through a hand-over buffer (g.x_ll): poll it instead of waiting at the grid barrier
     int next_attn = 0;                   // an attention stage follows; `at` holds its arguments (for the KV prefetch)
     int epi_cache = 0;                   // 1: EPI_RESIDUAL on the residual stream, 2: the fused QKV matrix -- per-thread state kept across layers (gemvdev::EpiCache)
@@ -146,13 +146,14 @@ struct MegaLaunch {
     uint32_t off_red = 0, off_xq = 0, off_xd = 0, off_xs = 0, off_att = 0, off_ring = 0, stage_bytes = 0;
     int ns = 0, att_max_local = 0;
     uint32_t pf_bytes = 0;               // L2 prefetch run-ahead per CTA, bytes (0 = off)
+    uint32_t ring_room = 0;              // shared memory left for the ring after the other buffers (set by mega_configure)
     int debug = 0;                       // tuning experiments (see mega.cu), results are wrong when set
     size_t smem_bytes = 0;
     TpPeers tp;                          // peers of the exchange stages (tp.n == 1: none)
 };
 bool mega_supported(int type, int grp, int head_dim);
 void mega_finish_stage(MegaStage& st, int grid);
-int mega_plan_stage(MegaStage& st, int ncw, int nb_max);
+int mega_plan_stage(MegaStage& st, int ncw, int nb_max, int tile_target = 0);      // tile_target: bytes per weight tile (0 = default)
 double mega_plan_cost(const QMat& W, int nb_max);      // estimated consumer cost of a matrix with at most nb_max units per lane
 int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s_max, int max_ctx);
 int mega_launch(const MegaLaunch& L, cudaStream_t stream);

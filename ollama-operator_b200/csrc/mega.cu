@@ -32,8 +32,12 @@ using namespace gemvdev;
 using namespace attndev;
 
 constexpr int MEGA_NS_MAX = 16;
-// Arrival units of a ring slot's `empty` barrier: every pair-slot owner warp of a tile arrives with
-// MEGA_EMPTY_BASE / (PT * S) units, so any tile shape with PT * S <= 15 owners completes the same barrier.
+// Arrival units of a ring slot's `empty` barrier: every WORKING warp of a stage (G * S of them, owner of a pair in the
+// tile or not) arrives with MEGA_EMPTY_BASE / (G * S) units, so any stage shape completes the same barrier.  A slot must
+// not be refilled before every worker has passed its wait on that tile's `full` barrier: a worker without a pair in the
+// tile holds nothing, but if the producer laps it (refills the slot before it has looked), its parity wait matches the
+// wrong phase and the kernel deadlocks.  (Seen at contexts beyond ~3800 with tiles of fewer pairs than workers: the KV
+// prefetch issued before the row loop staggers the warps by more than a tile there.)
 constexpr uint32_t MEGA_EMPTY_BASE = 360360;      // lcm(1..15)
 constexpr int MEGA_MAX_PAGES = 256;
 
@@ -466,7 +470,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const int PT = S.PT;
         const int npairs_cta = (r_end - r_begin) >> 1;
         const int ntiles = ((npairs_cta + PT - 1) * S.inv_PT) >> 16;             // ceil(npairs_cta / PT)
-        const uint32_t arrive_units = S.arrive_units;                            // MEGA_EMPTY_BASE / (PT * Sw)
+        const uint32_t arrive_units = S.arrive_units;                            // MEGA_EMPTY_BASE / (NW * Sw)
         long long c_wait = 0, c_work = 0;      // (trace only) cycles warp 0 spends waiting for tiles / computing
         if (tr) tr[14] = (unsigned long long)clock64();           // (stage set-up done, row loop starts)
         if (working) {
@@ -508,10 +512,8 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
                     if ((lane & 15) == 0) ysum[(2 * j + (upper ? 1 : 0)) * Sw + ch] = keep;
                 }
                 __syncwarp();
-                if (own) {
-                    if (lane == 0 && !(sm.debug & 2)) mbar_arrive_units(&empty[slot], arrive_units);   // this warp no longer reads the slot
-                    jn += NW;
-                }
+                if (lane == 0 && !(sm.debug & 2)) mbar_arrive_units(&empty[slot], arrive_units);   // this warp is past the slot (owner or not)
+                if (own) jn += NW;
                 if (tr) { const long long c2 = clock64(); c_wait += c1 - c0; c_work += c2 - c1; }
                 if (++slot == (uint32_t)sm.ns) { slot = 0; phase ^= 1u; }
             }
@@ -578,7 +580,7 @@ double mega_plan_cost(const QMat& W, int nb_max) {
     for (int nbe = kq ? 1 : nb_max; nbe >= 1; nbe--) best = std::min(best, plan_cost(nunits, nbe, MEGA_NCW, &S, &G));
     return best * (double)(W.rows / 2);
 }
-int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
+int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q, int tile_target) {
     const QMat& W = st.g.W;
     const bool kq = W.type == T_Q4_K || W.type == T_Q6_K;
     const int nb_max = kq ? 1 : nb_max_q;
@@ -599,7 +601,7 @@ int mega_plan_stage(MegaStage& st, int ncw, int nb_max_q) {
     // 46 KB / four); PT * S owner warps (<= 15) release a tile
     size_t rb = 0;
     for (int p = 0; p < W.n_planes; p++) rb += W.stride[p];
-    int pt = (int)((size_t)mega_tile_target() / (2 * rb));
+    int pt = (int)((size_t)(tile_target > 0 ? tile_target : mega_tile_target()) / (2 * rb));
     pt = std::max(1, std::min(pt, std::max(1, ncw / st.S)));
     st.PT = pt;
     st.RT = 2 * pt;
@@ -615,7 +617,7 @@ void mega_finish_stage(MegaStage& st, int grid) {
     st.pairs_rem = pairs % grid;
     st.inv_S = (65536 + st.S - 1) / st.S;
     st.inv_PT = (65536 + st.PT - 1) / st.PT;
-    st.arrive_units = MEGA_EMPTY_BASE / (uint32_t)(st.PT * st.S);
+    st.arrive_units = MEGA_EMPTY_BASE / (uint32_t)(st.G * st.S);
 }
 
 template <int TYPE, int NB, int NCW, int GRP, int HD, bool TP>
@@ -722,6 +724,7 @@ int mega_configure(MegaLaunch& L, int64_t k_max, size_t tile_bytes_max, int rt_s
         B2_TRY(q(&static_smem));
     }
     const size_t cap = (227 * 1024 - static_smem) / 128 * 128;          // 227 KB per CTA minus the kernel's static shared memory
+    L.ring_room = cap > off ? (uint32_t)(cap - off) : 0u;
     if (off + 2 * (size_t)L.stage_bytes > cap) B2_FAIL(B2_ERR_UNSUPPORTED, "mega: shared memory does not fit (%zu B before the ring, %u B per stage)", off, L.stage_bytes);
     L.ns = (int)std::min<size_t>(MEGA_NS_MAX, (cap - off) / L.stage_bytes);
     L.smem_bytes = off + (size_t)L.ns * L.stage_bytes;

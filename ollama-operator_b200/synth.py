@@ -60,7 +60,8 @@ PRESETS = {
     "tiny-phi2": ModelConfig(arch="phi2", n_embd=256, n_head=4, n_head_kv=4, n_ff=1024, n_rot=32),
     "tiny-phi2-80": ModelConfig(arch="phi2", n_embd=320, n_head=4, n_head_kv=4, n_ff=1280, n_rot=32),      # phi-2's head_dim 80
     "tiny-rope31": ModelConfig(rope_freq_base=500000.0, rope_scaling=4.0, rope_factors=True),   # Llama-3.1-style rope_freqs + linear scaling
-    "wide-llama-2l": ModelConfig(n_layer=2, n_embd=4096, n_head=32, n_head_kv=32, n_ff=11008, n_vocab=2048, n_ctx=512),      # 7B's widths, two layers (SURVEY 8c iv)
+    "wide-llama-2l": ModelConfig(n_layer=2, n_embd=4096, n_head=32, n_head_kv=32, n_ff=11008, n_vocab=2048, n_ctx=512),
+    "wide-llama-2l-long": ModelConfig(n_layer=2, n_embd=4096, n_head=32, n_head_kv=32, n_ff=11008, n_vocab=2048, n_ctx=4096),     # ... with room for a long context      # 7B's widths, two layers (SURVEY 8c iv)
     "wide13-llama-1l": ModelConfig(n_layer=1, n_embd=5120, n_head=40, n_head_kv=40, n_ff=13824, n_vocab=1024, n_ctx=256),     # 13B's widths: five activation units per lane, tiles smaller than a worker round
     "tiny-gqa8": ModelConfig(n_head=16, n_head_kv=2, n_embd=2048, n_ff=2048),      # 70B's head layout (8 query heads per KV head, head_dim 128), Q4_0
     "llama2-7b": ModelConfig(n_layer=32, n_embd=4096, n_head=32, n_head_kv=32, n_ff=11008, n_vocab=32000, n_ctx=4096, name="llama2-7b"),

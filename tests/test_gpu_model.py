@@ -290,3 +290,21 @@ def test_stage_handover_without_grid_barriers_keeps_the_bits(pkg, oracle, eng, m
     for name in ("barriers", "handover_h"):
         assert runs["handover"][0] == runs[name][0], name
         assert np.array_equal(runs["handover"][1], runs[name][1]), name
+
+
+def test_long_context_decode_does_not_lap_the_ring(pkg, eng, model_dir):
+    """Beyond ~3800 positions the KV prefetch issued before the QKV row loop staggers the warps of a CTA by more than one
+    weight tile.  With tiles of fewer row pairs than row workers a worker without a pair in a tile used to hold nothing,
+    the producer could refill the slot before that worker had looked at it, and its parity wait then matched the wrong
+    phase: the kernel deadlocked (reported as B2_ERR_CUDA by the spin guards after 4 s).  Decode across that range, and
+    compare with the per-matrix kernels."""
+    path = pkg.synth.cached_model("wide-llama-2l-long", model_dir, source="blocks")
+    toks = pkg.synth.prompt_tokens(3790, 2048, seed=9)
+    got = {}
+    for flags in (0, pkg.engine.LOAD_NO_MEGA):
+        m = eng.load(path, max_batch=1, max_ctx=3900, flags=flags)
+        seq = m.seq_new()
+        m.prefill(seq, toks, want_logits=False)
+        got[flags] = [int(t) for t in m.decode_greedy(seq, 60, first_tok=1)]
+        m.close()
+    assert got[0] == got[pkg.engine.LOAD_NO_MEGA]
