@@ -971,6 +971,7 @@ int Model::profile_step(int seq, int32_t tok, float* class_ms, int* class_launch
     int nl = 0;
     const bool saved = use_pdl;
     use_pdl = false;
+    B2_TRY(delay_launch(stream, 300000));      // the GPU idles 0.3 ms while the host enqueues: no launch gaps between the timed kernels
     const int rc = enqueue_step(s, true, &nl, &prof);
     use_pdl = saved;
     cudaStreamSynchronize(stream);

@@ -177,6 +177,7 @@ struct StepBeginArgs {
     MegaLaunch::LlInit ll_init;       // ... and the hand-over buffers its first writers use, poisoned every step
 };
 int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
+int delay_launch(cudaStream_t st, unsigned long long ns);      // a kernel that waits `ns` (profiling aid)
 struct StepEndArgs {
     SeqState* st = nullptr;
     const unsigned long long* argmax_key = nullptr;

@@ -44,6 +44,19 @@ int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl) {
     return B2_OK;
 }
 
+// A kernel that only waits: b2_profile_step queues it ahead of the step it times, so that the host has every launch of the
+// step enqueued before the GPU reaches the first one and the events between the kernels measure kernels, not launch gaps.
+__global__ void delay_kernel(unsigned long long ns) {
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    do { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); } while (t - t0 < ns);
+}
+int delay_launch(cudaStream_t st, unsigned long long ns) {
+    delay_kernel<<<1, 1, 0, st>>>(ns);
+    B2_CUDA(cudaGetLastError());
+    return B2_OK;
+}
+
 // step_end: pick the next token (prompt token while any are left, else the arg-max of the
 // logits), record it, advance the position.
 __global__ void step_end_kernel(const StepEndArgs a) {
