@@ -45,3 +45,17 @@ for k, nm in ((0, "qkv"), (2, "wo"), (3, "up"), (4, "down")):
     tail = (g[:, 3] - g[:, 2]) / 1e3 - loop
     print(f"body {nm}: warp 0 waits for tiles {(g[:, 12] / 1.9e3).mean():.2f} us, computes {(g[:, 13] / 1.9e3).mean():.2f} us")
     print(f"body {nm}: warp 0 row loop mean {loop.mean():.2f} max {loop.max():.2f} us; rest of the body (wait for the other warps + epilogue) mean {tail.mean():.2f} max {tail.max():.2f} us")
+
+# arrival spread: when each CTA enters / finishes a stage of layer 15, relative to the first one (us)
+for k in range(5):
+    s = 15 * 5 + k
+    ent, done = tr[:, s, 0] / 1e3, tr[:, s, 3] / 1e3
+    e, d = ent - ent.min(), done - done.min()
+    late = np.argsort(-d)[:6]
+    print(f"spread {names[k]:5s}: enter p50 {np.percentile(e, 50):5.2f} p90 {np.percentile(e, 90):5.2f} max {e.max():5.2f} | done p50 {np.percentile(d, 50):5.2f} p90 {np.percentile(d, 90):5.2f} max {d.max():5.2f}  latest CTAs {late.tolist()}")
+for L in (7, 15, 23):
+    g = tr[:, L * 5 + 3, :]
+    body = (g[:, 3] - g[:, 2]) / 1e3
+    wait = g[:, 12] / 1.9e3
+    order = np.argsort(-body)
+    print(f"up L{L}: slowest CTAs (cta body_us tile_wait_us):", [(int(c), round(float(body[c]), 2), round(float(wait[c]), 2)) for c in order[:8]], " median body", round(float(np.median(body)), 2), "median wait", round(float(np.median(wait)), 2))
