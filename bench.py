@@ -244,12 +244,12 @@ def run_gpu(args):
     # ---- end to end through b2_decode with host buffers: `e2e` ---------------------------------------
     last = int(toks[-1])
     for _ in range(3):
-        last = int(m.decode([seq], [last])[0])
+        last = m.decode_one(seq, last)
     barrier()
     t0 = time.perf_counter()
     e2e_gpu_ms = 0.0
     for _ in range(args.steps):
-        last = int(m.decode([seq], [last])[0])
+        last = m.decode_one(seq, last)       # b2_decode(1 sequence, host token in, host token out); the step's device time is read back too
         e2e_gpu_ms += m.stats().gpu_ms
     barrier()
     e2e_s = time.perf_counter() - t0

@@ -67,6 +67,7 @@ Model::~Model() {
     for (auto& s : slots) {
         if (s.g_full) cudaGraphExecDestroy(s.g_full);
         if (s.g_nohead) cudaGraphExecDestroy(s.g_nohead);
+        if (s.g_decode) cudaGraphExecDestroy(s.g_decode);
         if (s.d_stages) cudaFree(s.d_stages);
     }
     if (ev0) cudaEventDestroy(ev0);
@@ -759,6 +760,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
         StepBeginArgs a;
         a.st = s.d_state; a.embd = w_embd; a.x = s.x; a.pos_out = s.d_pos; a.argmax_key = s.d_key; a.grid_count = s.d_grid_count;
         if (s.mega_ok) a.ll_init = s.mega.ll_init;
+        a.st_host = s.zc_in;
         B2_TRY(step_begin_launch(a, stream, pdl)); nl++; B2_TRY(mark(0));
     }
     if (s.mega_ok) {
@@ -781,6 +783,7 @@ int Model::enqueue_step(Slot& s, bool with_head, int* n_launch, StepProfile* pro
     {
         StepEndArgs a;
         a.st = s.d_state; a.argmax_key = s.d_key; a.forced = s.d_forced; a.out_toks = s.d_out; a.out_cap = out_cap; a.use_argmax = with_head ? 1 : 0;
+        a.st_host = s.zc_out;
         B2_TRY(step_end_launch(a, stream, pdl)); nl++; B2_TRY(mark(7));
     }
     *n_launch = nl;
@@ -916,6 +919,40 @@ int Model::decode(int n_seq, const int* seqs, const int32_t* last_tok, int32_t* 
         B2_TRY(end_call(nullptr));
         for (int i = 0; i < n_seq; i++) slots[seqs[i]].len += 1;
         return B2_OK;
+    }
+    // One sequence, no logits (what a server does per generated token): the copy of the token in, the step and the copy of
+    // the state out are ONE graph, so the host enqueues a single launch -- every separately enqueued operation is GPU idle
+    // time here, because the GPU waits for the host between tokens (tp: the shards run this path in lock step, graphs are
+    // per shard, nothing changes).
+    if (n_seq == 1 && !logits && use_graph && slots[seqs[0]].warm_full && !tp_skip_reduce) {
+        Slot& s = slots[seqs[0]];
+        SeqState& st = pin_state[2 * seqs[0]];
+        st = SeqState{};
+        st.pos = s.len; st.cur_tok = last_tok[0];
+        if (!s.g_decode) {
+            cudaGraph_t graph = nullptr;
+            B2_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+            int nl = 0;
+            // (no copy nodes: step_begin reads the state from the pinned buffer, step_end writes the new one there -- two
+            //  copy-engine hops less per token)
+            s.zc_in = &st; s.zc_out = &pin_state[2 * seqs[0] + 1];
+            const int rc = enqueue_step(s, true, &nl, nullptr);
+            s.zc_in = s.zc_out = nullptr;
+            cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+            if (rc == B2_OK && ce == cudaSuccess) ce = cudaGraphInstantiate(&s.g_decode, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (rc != B2_OK || ce != cudaSuccess) { s.g_decode = nullptr; cudaGetLastError(); }
+            s.gl_full = nl > 0 ? nl : s.gl_full;
+        }
+        if (s.g_decode) {
+            B2_CUDA(cudaGraphLaunch(s.g_decode, stream));
+            launches += s.gl_full; last_launches += s.gl_full; steps += 1; last_steps += 1;
+            B2_TRY(end_call(nullptr));
+            s.host = pin_state[2 * seqs[0] + 1];
+            s.len += 1;
+            if (next_tok) next_tok[0] = s.host.cur_tok;
+            return B2_OK;
+        }
     }
     // the sequence state crosses the bus through pinned staging (pageable copies would each synchronise):
     // everything of this call is queued, then ONE synchronisation

@@ -58,6 +58,8 @@ struct Slot {
     MegaLaunch mega;
     MegaStage* d_stages = nullptr;
     cudaGraphExec_t g_full = nullptr, g_nohead = nullptr;
+    cudaGraphExec_t g_decode = nullptr;      // b2_decode of this one sequence: token in, step, state out as ONE graph launch
+    SeqState *zc_in = nullptr, *zc_out = nullptr;      // set while that graph is captured: state read from / written to pinned host memory by the step kernels
     int gl_full = 0, gl_nohead = 0;
     bool warm_full = false, warm_nohead = false;
 };

@@ -175,6 +175,7 @@ struct StepBeginArgs {
     unsigned long long* argmax_key = nullptr;
     unsigned* grid_count = nullptr;   // persistent kernel's barrier counter, cleared every step (may be null)
     MegaLaunch::LlInit ll_init;       // ... and the hand-over buffers its first writers use, poisoned every step
+    const SeqState* st_host = nullptr;   // when set: the step's input state, read straight from pinned host memory (no copy node)
 };
 int step_begin_launch(const StepBeginArgs& a, cudaStream_t st, bool pdl);
 int delay_launch(cudaStream_t st, unsigned long long ns);      // a kernel that waits `ns` (profiling aid)
@@ -185,6 +186,7 @@ struct StepEndArgs {
     int* out_toks = nullptr;       // ring of emitted tokens
     int out_cap = 0;
     int use_argmax = 1;            // 0: prompt step, the head did not run
+    SeqState* st_host = nullptr;   // when set: the resulting state is also written to pinned host memory (no copy node)
 };
 int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl);
 

@@ -14,7 +14,11 @@ namespace b2 {
 __global__ void step_begin_kernel(const StepBeginArgs a) {
     pdl_trigger();
     pdl_wait();
-    const int tok = a.st->cur_tok, pos = a.st->pos;
+    // b2_decode of one sequence hands the state over in pinned host memory: every block reads the two words it needs from
+    // there, block 0 also installs the state on the device for step_end
+    const SeqState* src = a.st_host ? a.st_host : a.st;
+    const int tok = src->cur_tok, pos = src->pos;
+    if (a.st_host && blockIdx.x == 0 && threadIdx.x == 0) *a.st = *a.st_host;
     const int E = (int)a.embd.k;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < E; i += gridDim.x * blockDim.x) a.x[i] = qmat_elem(a.embd, tok, i);
     // hand-over buffers of the persistent kernel (GemvArgs::x_ll): the ones written first in a step start out poisoned; done
@@ -75,6 +79,7 @@ __global__ void step_end_kernel(const StepEndArgs a) {
     }
     s->cur_tok = next;
     s->pos++;
+    if (a.st_host) { *a.st_host = *s; __threadfence_system(); }
 }
 
 int step_end_launch(const StepEndArgs& a, cudaStream_t st, bool pdl) {

@@ -261,6 +261,17 @@ class Model:
         _check(lib().b2_decode(self._h, seqs.size, _ptr(seqs), _ptr(last), _ptr(nxt), _ptr(logits)))
         return (nxt, logits) if want_logits else nxt
 
+    def decode_one(self, seq: int, last_tok: int) -> int:
+        """b2_decode for one sequence without logits, through preallocated host buffers: what a server calls per
+        generated token (no numpy conversions on the way, the C ABI call is the same)."""
+        buf = self.__dict__.get("_one")
+        if buf is None:
+            buf = self._one = ((C.c_int32 * 1)(), (C.c_int32 * 1)(), (C.c_int32 * 1)())
+        buf[0][0] = seq
+        buf[1][0] = last_tok
+        _check(lib().b2_decode(self._h, 1, buf[0], buf[1], buf[2], None))
+        return buf[2][0]
+
     def decode_greedy(self, seq: int, n_steps: int, first_tok: int = -1) -> np.ndarray:
         out = np.empty(n_steps, dtype=np.int32)
         _check(lib().b2_decode_greedy(self._h, seq, first_tok, n_steps, _ptr(out)))

@@ -308,3 +308,22 @@ def test_long_context_decode_does_not_lap_the_ring(pkg, eng, model_dir):
         got[flags] = [int(t) for t in m.decode_greedy(seq, 60, first_tok=1)]
         m.close()
     assert got[0] == got[pkg.engine.LOAD_NO_MEGA]
+
+
+def test_single_sequence_decode_graph_matches_the_general_path(pkg, eng, model_dir):
+    """b2_decode for one sequence without logits is one graph launch whose step kernels read the token from and write
+    the new state to pinned host memory; it must produce the tokens of the general path (and of decode_greedy)."""
+    path = pkg.synth.cached_model("tiny-llama", model_dir)
+    m = eng.load(path, max_batch=2, max_ctx=128)
+    toks = pkg.synth.prompt_tokens(12, m.info.n_vocab, seed=3)
+    a, b, c = m.seq_new(), m.seq_new(), None
+    la, lb = m.prefill(a, toks), m.prefill(b, toks)
+    ta = tb = int(np.argmax(la))
+    out_a, out_b = [], []
+    for _ in range(40):
+        ta = m.decode_one(a, ta); out_a.append(ta)
+        nb, _ = m.decode([b], [tb], want_logits=True); tb = int(nb[0]); out_b.append(tb)
+    assert out_a == out_b
+    m.seq_truncate(a, len(toks))
+    assert [int(t) for t in m.decode_greedy(a, 40, first_tok=int(np.argmax(la)))] == out_a
+    m.close()
