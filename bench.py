@@ -233,7 +233,7 @@ def run_gpu(args):
     # ---- device-resident loop: `value` ------------------------------------------------------------
     sampler = ClockSampler(local)
     sampler.start()
-    m.decode_greedy(seq, args.warmup)
+    wtoks = m.decode_greedy(seq, args.warmup)
     barrier()
     sampler.window_begin()
     toks = m.decode_greedy(seq, args.steps)
@@ -242,7 +242,12 @@ def run_gpu(args):
     gpu_ms, launches = st.gpu_ms, int(st.last_launches)
     ctx_mid = args.ctx + args.warmup + args.steps // 2
     # ---- end to end through b2_decode with host buffers: `e2e` ---------------------------------------
+    # ... over the SAME positions as `value`: the sequence is cut back to three steps before the timed region started (the
+    # cache rows are simply written again, with the same bits), so that both numbers see the same context lengths
     last = int(toks[-1])
+    if args.warmup >= 4:
+        m.seq_truncate(seq, args.ctx + args.warmup - 3)
+        last = int(wtoks[args.warmup - 4])
     for _ in range(3):
         last = m.decode_one(seq, last)
     barrier()
