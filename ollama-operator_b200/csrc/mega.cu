@@ -258,12 +258,12 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
     unsigned tp_epoch = TP ? *reinterpret_cast<volatile unsigned*>(tp.epoch) : 0u;      // exchanges completed before this launch
     // Hand-over buffers (GemvArgs::x_ll): write number w of a vector goes to buffer w % NB of its rotation, and the thread
     // that stores row r of write w puts the poison back into row r of the buffer of write w - 1.
-    //  * Nobody reads that buffer any more: its readers are the prologue of the stage after write w - 1, and the writer
-    //    of w is past its own prologue (or the QKV -> attention barrier), which needed every CTA's output of a stage after
-    //    that prologue.
-    //  * The poison is visible before that buffer is polled again (for write w - 1 + NB): the QKV -> attention grid
-    //    barrier of the next layer lies in between.  att and h are written once per layer (NB = 2 is enough); x is
-    //    written twice (by wo and down), so its rotation has NB = 3 buffers to put a barrier between poison and poll.
+    //  * Nobody reads that buffer any more: its readers are the prologue of the stage after write w - 1 (for the q/k/v
+    //    hand-over: the attention stage), and the writer of w is past its own prologue, which needed every CTA's output
+    //    of a stage after that one.
+    //  * The poison is visible before that buffer is polled again (for write w - 1 + NB): a grid barrier lies in between
+    //    -- up -> down, the one barrier a layer keeps.  att, h and q/k/v are written once per layer (NB = 2 is enough); x
+    //    is written twice (by wo and down), so its rotation has NB = 3 buffers to put that barrier between poison and poll.
     //  * The buffers of the first NB - 1 writes of a launch are poisoned by the kernel that precedes this one (step_begin).
     double* ysum = red;                                   // per-row partial sums of this CTA's rows: [row_local][S]
     bool res_valid = false, rope_valid = false;          // the caches above hold this launch's values
