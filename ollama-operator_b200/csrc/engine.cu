@@ -677,7 +677,8 @@ int Model::setup_mega(Slot& s) {
             const GemvArgs& g = c.g;
             const bool fast = (g.W.type == T_Q4_0 || g.W.type == T_Q8_0) && (g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 256 == 0 &&
                               g.W.k / 4 <= (int64_t)8 * MEGA_NCW * 32;          // the kernel's fast prologue path (mega.cu)
-            if (!fast) continue;
+            // (a stage outside the fast path -- K-quants, very long vectors -- polls the buffer complete and then runs its generic prologue on it)
+            if (!fast && !((g.pro == PRO_PLAIN || g.pro == PRO_RMSNORM) && g.W.k % 4 == 0 && !getenv("B2_MEGA_NO_LL_GENERIC"))) continue;
             if (p.kind == 1 && p.at.out == g.x && g.W.k == (int64_t)hp.n_head * hp.head_dim) {
                 p.at.out_ll = s.att_ll[wa & 1]; p.at.out_ll_poison = s.att_ll[(wa + 1) & 1]; c.g.x_ll = s.att_ll[wa & 1]; c.ll_in = 1; wa++;
             } else if (p.kind == 0 && p.g.epi == EPI_RESIDUAL && p.g.y == g.x && p.g.epi_row0 == 0 && p.g.W.rows == g.W.k && g.W.k == hp.n_embd) {

@@ -31,6 +31,13 @@ static __device__ double consumers_sum(double v, double* scratch, int tid, int n
     return s;
 }
 
+// Four values of the stage input.  In the persistent kernel a stage may read a hand-over buffer (GemvArgs::x_ll) that other
+// SMs wrote during this launch with no L1 invalidation in between: those reads go to L2 (the caller has polled the buffer
+// complete before).  Everywhere else x was written by an earlier kernel and the plain load stands.
+__device__ __forceinline__ float4 load_x4(const GemvArgs& a, int i) {
+    return a.x_ll ? ll_load4(a.x_ll + i) : *reinterpret_cast<const float4*>(a.x + i);
+}
+
 static __device__ ProStats prologue_stats(const GemvArgs& a, double* scratch, int tid, int ntc) {
     ProStats st{0.f, 1.f};
     const int K = (int)a.W.k;
@@ -38,7 +45,7 @@ static __device__ ProStats prologue_stats(const GemvArgs& a, double* scratch, in
         // ggml rms_norm: f64 sum of f32 squares; scale = 1/sqrtf(mean + eps)
         double ss = 0;
         for (int i = tid * 4; i < K; i += ntc * 4) {
-            const float4 v = *reinterpret_cast<const float4*>(a.x + i);
+            const float4 v = load_x4(a, i);
             ss += (double)__fmul_rn(v.x, v.x); ss += (double)__fmul_rn(v.y, v.y);
             ss += (double)__fmul_rn(v.z, v.z); ss += (double)__fmul_rn(v.w, v.w);
         }
@@ -49,14 +56,14 @@ static __device__ ProStats prologue_stats(const GemvArgs& a, double* scratch, in
         // ggml norm: mean, then centred sum of squares, both in f64
         double s = 0;
         for (int i = tid * 4; i < K; i += ntc * 4) {
-            const float4 v = *reinterpret_cast<const float4*>(a.x + i);
+            const float4 v = load_x4(a, i);
             s += (double)v.x; s += (double)v.y; s += (double)v.z; s += (double)v.w;
         }
         s = consumers_sum(s, scratch, tid, ntc);
         st.mean = (float)(s / (double)K);
         double ss = 0;
         for (int i = tid * 4; i < K; i += ntc * 4) {
-            const float4 v = *reinterpret_cast<const float4*>(a.x + i);
+            const float4 v = load_x4(a, i);
             const float c0 = __fsub_rn(v.x, st.mean), c1 = __fsub_rn(v.y, st.mean), c2 = __fsub_rn(v.z, st.mean), c3 = __fsub_rn(v.w, st.mean);
             ss += (double)__fmul_rn(c0, c0); ss += (double)__fmul_rn(c1, c1);
             ss += (double)__fmul_rn(c2, c2); ss += (double)__fmul_rn(c3, c3);
@@ -69,7 +76,7 @@ static __device__ ProStats prologue_stats(const GemvArgs& a, double* scratch, in
 }
 
 __device__ __forceinline__ float4 prologue_vals(const GemvArgs& a, const ProStats& st, int i) {
-    float4 v = *reinterpret_cast<const float4*>(a.x + i);
+    float4 v = load_x4(a, i);
     if (a.pro == PRO_RMSNORM) {
         const float4 g = *reinterpret_cast<const float4*>(a.gain + i);
         v.x = __fmul_rn(__fmul_rn(v.x, st.scale), g.x); v.y = __fmul_rn(__fmul_rn(v.y, st.scale), g.y);

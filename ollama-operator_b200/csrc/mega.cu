@@ -327,7 +327,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
         const bool fast = (TYPE == T_Q4_0 || TYPE == T_Q8_0) && a.pro != PRO_LAYERNORM && nchunks <= ntc * MAXC && (K & 255) == 0;
         // ll_in: the input vector carries the producing stage's tag next to every value; polling those replaces the barrier
         // (and the next descriptor is fetched further down, once every thread of this CTA is known to have left the previous stage)
-        const bool ll_in = !TP && S.ll_in != 0 && fast;
+        const bool ll_in = !TP && S.ll_in != 0;
         auto stage_barrier = [&]() {
             if (!ll_in) {
                 if (st > s_begin) grid_barrier(grid_count, epoch, tid, ntc);     // the previous stage's outputs are complete and visible
@@ -445,6 +445,16 @@ __global__ void __launch_bounds__((NCW + 1) * 32, 1) mega_kernel(const MegaStage
             }
         } else {
             stage_barrier();
+            if (ll_in) {
+                // generic prologue over a hand-over buffer: first see every chunk final (each thread polls a share), then
+                // run the usual passes, whose loads of x go to L2 (gemvdev::load_x4)
+                for (int i = tid * 4; i < K; i += ntc * 4) {
+                    float4 v = ll_load4(a.x_ll + i);
+                    SpinGuard guard;
+                    while (!ll_ready(v)) { v = ll_load4(a.x_ll + i); guard.tick(); }
+                }
+                named_bar_sync(1, ntc);
+            }
             const ProStats ps = prologue_stats(a, dscratch, tid, ntc);
             if (TYPE == T_Q4_0 || TYPE == T_Q8_0) prologue_q8_0(a, ps, xq, xd, xs, tid, ntc);
             else prologue_q8_K(a, ps, xq, xd, xs, tid, ntc);
